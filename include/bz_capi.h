@@ -1,0 +1,161 @@
+/* bz_capi.h -- C ABI of the B200-native Bezier-triangle intersect/refract path.
+ *
+ * This is the drop-in boundary for ONE hot path of balazs-bamer/cuda-bezier-triangle-raytracer:
+ *   BezierLens::refract          reference/bezierLens.h:27,  bezierLens.cpp:4-34
+ *   -> BezierMesh::intersect     reference/bezierMesh.h:37,  bezierMesh.cpp:206-227
+ *   -> BezierTriangle::intersect reference/bezierTriangle.h:105, bezierTriangle.cpp:123-195
+ * plus the ray-generation / bounce-loop / shading stages the reference never wrote
+ * (reference/rayTracer.cpp is empty; the loop shape follows reference/test.cpp:376-398).
+ *
+ * Plain pointers and sizes only.  Every function returns BZ_OK (0) or a negative error code;
+ * bz_last_error() gives the text for the calling thread.  There is no CPU fallback: every entry
+ * point that computes needs a CUDA device and fails loudly without one.
+ *
+ * Pointers named d_* are DEVICE pointers, h_* are HOST pointers.  `stream` is a cudaStream_t
+ * passed as void* (NULL = the legacy default stream).  Calls taking a stream are asynchronous
+ * on it; *_host calls are synchronous and include the host<->device copies.
+ */
+#ifndef BZ_CAPI_H
+#define BZ_CAPI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BZ_OK                 0
+#define BZ_ERR_INVALID       -1   /* bad argument */
+#define BZ_ERR_CUDA          -2   /* CUDA runtime error, see bz_last_error() */
+#define BZ_ERR_NO_DEVICE     -3   /* no usable CUDA device: there is no CPU path */
+#define BZ_ERR_PREPROCESS    -4   /* mesh preprocessing threw (e.g. "Vertex on edge detected.", reference/mesh.cpp:204) */
+
+/* RefractionResult, reference/bezierLens.h:7-11 */
+#define BZ_STATUS_NONE        0u
+#define BZ_STATUS_INSIDE      1u
+#define BZ_STATUS_OUTSIDE     2u
+
+/* BezierIntersection::What, reference/bezierTriangle.h:8-14 (batch intersect reports NONE or INTERSECT) */
+#define BZ_WHAT_NONE          3u
+#define BZ_WHAT_INTERSECT     4u
+
+#define BZ_NO_PATCH  0xffffffffu
+
+/* POD mirror of the per-patch record BezierTriangle holds (reference/bezierTriangle.h:64-80).
+ * mBezierDerivativeDirectionVectorA is the constant (1,0,-1) (bezierTriangle.cpp:83) and is not
+ * stored.  256 bytes, 16-byte aligned. */
+typedef struct bz_patch {
+  float    plane[4];         /* mUnderlyingPlane: unit normal xyz, constant        (h:64) */
+  float    divider[3][4];    /* mNeighbourDividerPlanes[i]: normal xyz, constant   (h:65) */
+  uint32_t neighbours[3];    /* mNeighbours, patch indices after Clough-Tocher     (h:68) */
+  float    height_inside;    /* mHeightInside  (< 0, already x1.3333)              (h:77) */
+  float    control[10][3];   /* mControlPoints, index map h:31-51                  (h:73) */
+  float    height_outside;   /* mHeightOutside (> 0, already x1.3333)              (h:78) */
+  float    dir_b[3];         /* mBezierDerivativeDirectionVectorB                  (h:80) */
+  float    bary_inv[3][3];   /* mBarycentricInverse, row-major: b = bary_inv * P   (h:75) */
+  float    reserved[1];
+} bz_patch;
+
+/* Camera of the headless renderer (no reference counterpart; definitions in DESIGN.md).
+ * Sample (px,py,sx,sy), strata S:  fu = px + (sx+0.5)/S, fv = py + (sy+0.5)/S,
+ *   a = (fu*(2/width) - 1)*half_w,  b = (1 - fv*(2/height))*half_h
+ * pinhole: start = eye,                     dir = normalize(forward + (right*a + up*b))
+ * ortho:   start = eye + (right*a + up*b),  dir = normalize(forward)                      */
+typedef struct bz_camera {
+  float    eye[3];
+  float    forward[3];
+  float    right[3];
+  float    up[3];
+  float    half_w;
+  float    half_h;
+  uint32_t width;
+  uint32_t height;
+  uint32_t strata;           /* samples per pixel = strata*strata, fixed stratified grid, no jitter */
+  uint32_t ortho;            /* 0 = pinhole, 1 = orthographic */
+} bz_camera;
+
+/* Scene behind the lens + bounce-loop limit. */
+typedef struct bz_scene {
+  float    bg_plane[4];      /* background plane: unit normal xyz, constant (Plane semantics, 3dGeomUtil.h:279-296) */
+  float    bg_axis_a[3];     /* checker coordinate axes: ia = floor((P . axis_a)/cell) */
+  float    bg_axis_b[3];
+  float    cell;
+  uint32_t value_dark;       /* checker values, 0..255 */
+  uint32_t value_bright;
+  uint32_t value_lost;       /* ray entered and never left, or never reached the background */
+  uint32_t max_crossings;    /* bounce loop: at most this many refract() calls per primary ray */
+} bz_scene;
+
+/* Work counters: executed work, never brute-force-equivalent work. */
+typedef struct bz_stats {
+  uint64_t primary_rays;
+  uint64_t refract_calls;    /* surface-crossing attempts = BezierLens::refract calls */
+  uint64_t stage_a;          /* plane + barycentric tests executed  (bezierTriangle.cpp:124-131) */
+  uint64_t stage_b;          /* Newton evaluations executed incl. follow hops (cpp:132-194) */
+  uint64_t snell;            /* calls that reached the Snell block (bezierLens.cpp:8-27) */
+  uint64_t entered;          /* refract() returned cInside */
+  uint64_t exited;           /* refract() returned cOutside */
+  uint64_t lost;             /* primary rays shaded value_lost */
+} bz_stats;
+
+typedef struct bz_lens bz_lens;
+
+/* intersect strategy of a lens handle */
+#define BZ_MODE_BRUTE   0u   /* every ray tests every patch, reference loop order (bezierMesh.cpp:211) */
+#define BZ_MODE_CULLED  1u   /* exact candidate-set-preserving packet cull, then the same stage A/B */
+
+const char *bz_last_error(void);
+int  bz_device_count(int *out_count);
+/* size/offset self-check so a foreign-language binding can verify its struct mirrors */
+uint32_t bz_sizeof_patch(void);
+uint32_t bz_sizeof_camera(void);
+uint32_t bz_sizeof_scene(void);
+uint32_t bz_sizeof_stats(void);
+
+/* BezierLens(float aRi, BezierMesh const&)  -- reference/bezierLens.h:23-24.
+ * Uploads the patch records to `device`, repacks them into SoA float4 streams and builds the
+ * cull hierarchy.  h_patches is read during the call only. */
+int  bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refractive_index, int device, bz_lens **out_lens);
+int  bz_lens_destroy(bz_lens *lens);
+int  bz_lens_set_mode(bz_lens *lens, uint32_t mode);
+int  bz_lens_patch_count(const bz_lens *lens, uint32_t *out_count);
+
+/* BezierLens::refract over a batch  -- reference/bezierLens.h:27, bezierLens.cpp:4-34.
+ * start/dir: n x 3 floats (dir must be unit length, as Ray::Ray leaves it, 3dGeomUtil.h:176-178).
+ * expected: n x u32 (BZ_STATUS_*).  out_status == BZ_STATUS_NONE leaves out_start/out_dir of that
+ * ray equal to the input ray.  d_out_patch (nullable): index of the hit patch or BZ_NO_PATCH. */
+int  bz_refract_batch(bz_lens *lens, const float *d_start, const float *d_dir, const uint32_t *d_expected, uint64_t n,
+                      float *d_out_start, float *d_out_dir, uint32_t *d_out_status, uint32_t *d_out_patch, void *stream);
+int  bz_refract_batch_host(bz_lens *lens, const float *h_start, const float *h_dir, const uint32_t *h_expected, uint64_t n,
+                           float *h_out_start, float *h_out_dir, uint32_t *h_out_status, uint32_t *h_out_patch);
+
+/* BezierMesh::intersect over a batch  -- reference/bezierMesh.h:37, bezierMesh.cpp:206-227.
+ * Outputs (all nullable except d_out_what): what (BZ_WHAT_*), patch, distance, point[3],
+ * normal[3], cos incidence, barycentric[3]. */
+int  bz_intersect_batch(bz_lens *lens, const float *d_start, const float *d_dir, uint64_t n,
+                        uint32_t *d_out_what, uint32_t *d_out_patch, float *d_out_distance, float *d_out_point,
+                        float *d_out_normal, float *d_out_cos, float *d_out_bary, void *stream);
+int  bz_intersect_batch_host(bz_lens *lens, const float *h_start, const float *h_dir, uint64_t n,
+                             uint32_t *h_out_what, uint32_t *h_out_patch, float *h_out_distance, float *h_out_point,
+                             float *h_out_normal, float *h_out_cos, float *h_out_bary);
+
+/* K1: primary rays of image rows [row0,row1), pixel-major then sample-major:
+ * ray index = ((py-row0)*width + px)*spp + (sy*strata + sx).  Outputs n x 3 floats each. */
+int  bz_generate_rays(const bz_camera *camera, uint32_t row0, uint32_t row1, float *d_start, float *d_dir, void *stream);
+
+/* K1+K2+K3: render rows [row0,row1) into d_rgba ((row1-row0) x width x 4 bytes, row-major,
+ * R=G=B=value, A=255).  d_stats (nullable) is ACCUMULATED into (device memory, caller zeroes). */
+int  bz_render(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
+               uint8_t *d_rgba, bz_stats *d_stats, void *stream);
+int  bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
+                    uint8_t *h_rgba, bz_stats *h_stats);
+
+/* Device time (ms) of the intersect/refract kernels of the most recent bz_render / bz_refract_batch
+ * on this lens, measured with CUDA events on the stream the call used; synchronises that stream. */
+int  bz_last_kernel_ms(bz_lens *lens, float *out_ms);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif
