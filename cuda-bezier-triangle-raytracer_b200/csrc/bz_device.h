@@ -1,0 +1,69 @@
+// bz_device.h -- layout of the patch tables in HBM and the job descriptors the kernels take.
+//
+// Tables (all 16-byte aligned float4 streams, built once per lens by bz_lens_create):
+//   cull     4 float4 per patch, ORIGINAL patch order   stage-A record  (bezierTriangle.h:64,75,77-78)
+//            [0] plane n.xyz, k   [1] Binv row0.xyz, hIn   [2] Binv row1.xyz, hOut   [3] Binv row2.xyz, patch index bits
+//   newton  12 float4 per patch, ORIGINAL patch order   stage-B record  (bezierTriangle.h:65,68,73,80)
+//            words 0..29 control points, 30..32 dirB, 33..44 divider planes (n.xyz,k) x3, 45..47 neighbours
+//   leaf     4 float4 per leaf slot: the cull records again, in BVH leaf order, followed by the
+//            "always" segment (patches the cull cannot bound, tested for every ray)
+//   nodes    8 float4 per 4-wide BVH node: lo.x[4] hi.x[4] lo.y[4] hi.y[4] lo.z[4] hi.z[4] child[4] pad
+//            child > 0: inner node index; child < 0: leaf, ~child = first_slot << 3 | count; 0: empty
+#ifndef BZ_DEVICE_H
+#define BZ_DEVICE_H
+
+#include <stdint.h>
+#include <cuda_runtime.h>
+#include "bz_capi.h"
+
+#define BZ_CULL_F4    4
+#define BZ_NEWTON_F4  12
+#define BZ_NODE_F4    8
+#define BZ_LEAF_MAX   4
+
+struct bz_tables {
+  const float4 *cull;
+  const float4 *newton;
+  const float4 *leaf;
+  const float4 *nodes;
+  uint32_t patch_count;
+  uint32_t node_count;
+  uint32_t always_first;   // slot range [always_first, always_first + always_count) of `leaf`
+  uint32_t always_count;
+  float    ri;
+  float    extent;         // max |coordinate| over the flat triangles: sizes the per-ray cull slack
+};
+
+#define BZ_JOB_RENDER     0
+#define BZ_JOB_REFRACT    1
+#define BZ_JOB_INTERSECT  2
+
+struct bz_job {
+  // BZ_JOB_RENDER
+  bz_camera camera;
+  bz_scene  scene;
+  uint32_t  row0;            // first image row of this call
+  uint32_t  stripe_rows;     // 0: rows [row0,row0+rows) contiguous; else striped: local row r is image row
+  uint32_t  stripe_rank;     //    ((r / stripe_rows) * stripe_ranks + stripe_rank) * stripe_rows + r % stripe_rows
+  uint32_t  stripe_ranks;
+  uint32_t *accum;           // one u32 per local pixel: sum of the sample values
+  // BZ_JOB_REFRACT / BZ_JOB_INTERSECT
+  const float    *in_start;
+  const float    *in_dir;
+  const uint32_t *in_expected;
+  float    *out_start;
+  float    *out_dir;
+  uint32_t *out_status;      // refract: status; intersect: what
+  uint32_t *out_patch;
+  float    *out_distance;
+  float    *out_point;
+  float    *out_normal;
+  float    *out_cos;
+  float    *out_bary;
+  // all
+  uint64_t  ray_count;       // primary rays of this call
+  unsigned long long *next_ray;   // work counter, zeroed before launch
+  unsigned long long *stats;      // 9 counters in bz_stats order, accumulated; nullable
+};
+
+#endif

@@ -96,6 +96,7 @@ typedef struct bz_stats {
   uint64_t entered;          /* refract() returned cInside */
   uint64_t exited;           /* refract() returned cOutside */
   uint64_t lost;             /* primary rays shaded value_lost */
+  uint64_t node_visits;      /* 4-wide cull-hierarchy nodes visited (0 in BZ_MODE_BRUTE) */
 } bz_stats;
 
 typedef struct bz_lens bz_lens;
