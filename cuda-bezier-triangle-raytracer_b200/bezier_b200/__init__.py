@@ -1,0 +1,259 @@
+"""bezier_b200 -- Python face of libbz_b200.so (include/bz_capi.h), the B200-native
+Bezier-triangle intersect/refract path.
+
+The classes mirror the reference's host API for this path (reference/mesh.h, bezierMesh.h,
+bezierLens.h): Mesh -> BezierMesh -> BezierLens.refract.  All arithmetic of the hot path runs in
+the hand-written sm_100a kernels behind the C ABI; this module only moves pointers.  There is no
+CPU path: without the built library or without a CUDA device every computing call raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libbz_b200.so")
+
+OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_PREPROCESS = 0, -1, -2, -3, -4
+STATUS_NONE, STATUS_INSIDE, STATUS_OUTSIDE = 0, 1, 2
+WHAT_NONE, WHAT_INTERSECT = 3, 4
+NO_PATCH = 0xFFFFFFFF
+MODE_BRUTE, MODE_CULLED = 0, 1
+PATCH_WORDS = 64
+
+
+class BezierError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__("libbz_b200 error %d: %s" % (code, text))
+        self.code = code
+
+
+class Camera(C.Structure):
+    """bz_camera (include/bz_capi.h)"""
+    _fields_ = [("eye", C.c_float * 3), ("forward", C.c_float * 3), ("right", C.c_float * 3), ("up", C.c_float * 3),
+                ("half_w", C.c_float), ("half_h", C.c_float),
+                ("width", C.c_uint32), ("height", C.c_uint32), ("strata", C.c_uint32), ("ortho", C.c_uint32)]
+
+
+class Scene(C.Structure):
+    """bz_scene (include/bz_capi.h)"""
+    _fields_ = [("bg_plane", C.c_float * 4), ("bg_axis_a", C.c_float * 3), ("bg_axis_b", C.c_float * 3),
+                ("cell", C.c_float), ("value_dark", C.c_uint32), ("value_bright", C.c_uint32),
+                ("value_lost", C.c_uint32), ("max_crossings", C.c_uint32)]
+
+
+STAT_NAMES = ("primary_rays", "refract_calls", "stage_a", "stage_b", "snell", "entered", "exited", "lost", "node_visits")
+
+
+class Stats(C.Structure):
+    """bz_stats (include/bz_capi.h)"""
+    _fields_ = [(n, C.c_uint64) for n in STAT_NAMES]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n in STAT_NAMES}
+
+
+def make_camera(width, height, strata=1, eye=(-12.0, 0.0, 0.0), half_w=0.5, half_h=None, ortho=False,
+                forward=(1.0, 0.0, 0.0), right=(0.0, 1.0, 0.0), up=(0.0, 0.0, 1.0)):
+    cam = Camera()
+    cam.eye[:] = eye
+    cam.forward[:] = forward
+    cam.right[:] = right
+    cam.up[:] = up
+    cam.half_w = half_w
+    cam.half_h = half_w * height / width if half_h is None else half_h
+    cam.width, cam.height, cam.strata, cam.ortho = width, height, strata, 1 if ortho else 0
+    return cam
+
+
+def make_scene(bg_x=12.0, cell=1.0, dark=25, bright=230, lost=0, max_crossings=2):
+    sc = Scene()
+    sc.bg_plane[:] = (1.0, 0.0, 0.0, bg_x)
+    sc.bg_axis_a[:] = (0.0, 1.0, 0.0)
+    sc.bg_axis_b[:] = (0.0, 0.0, 1.0)
+    sc.cell = cell
+    sc.value_dark, sc.value_bright, sc.value_lost, sc.max_crossings = dark, bright, lost, max_crossings
+    return sc
+
+
+_lib = None
+
+_vp, _f, _u32, _i32, _u64, _int = C.c_void_p, C.c_float, C.c_uint32, C.c_int32, C.c_uint64, C.c_int
+
+# every symbol include/bz_capi.h declares: name -> (restype, argtypes)
+SIGNATURES = {
+    "bz_last_error": (C.c_char_p, []),
+    "bz_device_count": (_int, [C.POINTER(_int)]),
+    "bz_sizeof_patch": (_u32, []),
+    "bz_sizeof_camera": (_u32, []),
+    "bz_sizeof_scene": (_u32, []),
+    "bz_sizeof_stats": (_u32, []),
+    "bz_lens_create": (_int, [_vp, _u32, _f, _int, C.POINTER(_vp)]),
+    "bz_lens_destroy": (_int, [_vp]),
+    "bz_lens_set_mode": (_int, [_vp, _u32]),
+    "bz_lens_patch_count": (_int, [_vp, C.POINTER(_u32)]),
+    "bz_lens_info": (_int, [_vp, C.POINTER(_u32 * 4)]),
+    "bz_refract_batch": (_int, [_vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
+    "bz_refract_batch_host": (_int, [_vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
+    "bz_intersect_batch": (_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "bz_intersect_batch_host": (_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "bz_generate_rays": (_int, [C.POINTER(Camera), _u32, _u32, _vp, _vp, _vp]),
+    "bz_render": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _vp, _vp, _vp]),
+    "bz_render_host": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _vp, C.POINTER(Stats)]),
+    "bz_striped_rows": (_u32, [_u32, _u32, _u32, _u32]),
+    "bz_render_striped": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _u32, _vp, _vp, _vp]),
+    "bz_fp32_peak_probe": (_int, [_int, C.POINTER(_f), C.POINTER(_f)]),
+    "bz_last_kernel_ms": (_int, [_vp, C.POINTER(_f)]),
+}
+
+
+def load():
+    """Load libbz_b200.so; raises if it has not been built (there is no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("libbz_b200.so is not built: run `make -C %s` (or __graft_entry__.build())" % os.path.dirname(LIB_PATH))
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _check(rc):
+    if rc != OK:
+        raise BezierError(rc, load().bz_last_error().decode())
+
+
+def device_count():
+    n = _int(0)
+    _check(load().bz_device_count(C.byref(n)))
+    return n.value
+
+
+def fp32_peak_probe(device=0):
+    """(TFLOP/s, ms) of the dependent-FMA probe kernel on `device`."""
+    tf, ms = _f(0.0), _f(0.0)
+    _check(load().bz_fp32_peak_probe(device, C.byref(tf), C.byref(ms)))
+    return tf.value, ms.value
+
+
+def striped_rows(height, stripe_rows, rank, ranks):
+    return int(load().bz_striped_rows(height, stripe_rows, rank, ranks))
+
+
+def _np(a, dtype, shape):
+    return np.ascontiguousarray(a, dtype=dtype).reshape(shape)
+
+
+def _ptr(t):
+    """device pointer of a torch tensor (or None)"""
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream_handle(stream):
+    if stream is None:
+        import torch
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return C.c_void_p(int(stream))
+
+
+class BezierLens:
+    """BezierLens(ri, bezier_mesh) -- reference/bezierLens.h:14-28.
+
+    `patches` is either a BezierMesh of this package or an (n, 64) float32 array of bz_patch
+    records.  The lens owns the SoA tables and the cull hierarchy on `device`."""
+
+    def __init__(self, ri, patches, device=0):
+        self.lib = load()
+        table = patches.patches() if hasattr(patches, "patches") else patches
+        table = np.ascontiguousarray(table, dtype=np.float32)
+        if table.size == 0:
+            table = table.reshape(0, PATCH_WORDS)
+        assert table.ndim == 2 and table.shape[1] == PATCH_WORDS
+        self.device = device
+        self.ri = float(ri)
+        self.patch_count = table.shape[0]
+        handle = _vp()
+        _check(self.lib.bz_lens_create(table.ctypes.data_as(_vp), table.shape[0], self.ri, device, C.byref(handle)))
+        self.h = handle
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.bz_lens_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_mode(self, mode):
+        _check(self.lib.bz_lens_set_mode(self.h, mode))
+        return self
+
+    def info(self):
+        out = (_u32 * 4)()
+        _check(self.lib.bz_lens_info(self.h, C.byref(out)))
+        return dict(nodes=out[0], levels=out[1], always=out[2], sm_count=out[3])
+
+    def last_kernel_ms(self):
+        ms = _f(0.0)
+        _check(self.lib.bz_last_kernel_ms(self.h, C.byref(ms)))
+        return ms.value
+
+    # ---- host-buffer entry points (numpy in, numpy out; copies inside the call) ----
+
+    def refract(self, start, direction, expected):
+        """BezierLens::refract over a batch of host rays -> (start, dir, status, patch)"""
+        s, d = _np(start, np.float32, (-1, 3)), _np(direction, np.float32, (-1, 3))
+        n = s.shape[0]
+        e = np.ascontiguousarray(np.broadcast_to(np.asarray(expected, np.uint32), (n,)))
+        os_, od = np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+        st, pa = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        p = lambda a: a.ctypes.data_as(_vp)
+        _check(self.lib.bz_refract_batch_host(self.h, p(s), p(d), p(e), n, p(os_), p(od), p(st), p(pa)))
+        return os_, od, st, pa
+
+    def intersect(self, start, direction):
+        """BezierMesh::intersect over a batch of host rays -> dict"""
+        s, d = _np(start, np.float32, (-1, 3)), _np(direction, np.float32, (-1, 3))
+        n = s.shape[0]
+        what, patch = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        dist, cos = np.zeros(n, np.float32), np.zeros(n, np.float32)
+        point, normal, bary = (np.zeros((n, 3), np.float32) for _ in range(3))
+        p = lambda a: a.ctypes.data_as(_vp)
+        _check(self.lib.bz_intersect_batch_host(self.h, p(s), p(d), n, p(what), p(patch), p(dist), p(point), p(normal), p(cos), p(bary)))
+        return dict(what=what, patch=patch, distance=dist, point=point, normal=normal, cos=cos, bary=bary)
+
+    def render(self, camera, scene, row0=0, row1=None):
+        """host image of rows [row0,row1): (rows, width, 4) uint8, Stats"""
+        row1 = camera.height if row1 is None else row1
+        rgba = np.zeros((row1 - row0, camera.width, 4), np.uint8)
+        stats = Stats()
+        _check(self.lib.bz_render_host(self.h, C.byref(camera), C.byref(scene), row0, row1, rgba.ctypes.data_as(_vp), C.byref(stats)))
+        return rgba, stats
+
+    # ---- device-buffer entry points (torch CUDA tensors, asynchronous on the stream) ----
+
+    def refract_device(self, start, direction, expected, out_start, out_dir, out_status, out_patch=None, stream=None):
+        n = start.shape[0]
+        _check(self.lib.bz_refract_batch(self.h, _ptr(start), _ptr(direction), _ptr(expected), n, _ptr(out_start), _ptr(out_dir),
+                                         _ptr(out_status), _ptr(out_patch), _stream_handle(stream)))
+
+    def render_device(self, camera, scene, rgba, row0=0, row1=None, stats=None, stream=None):
+        row1 = camera.height if row1 is None else row1
+        _check(self.lib.bz_render(self.h, C.byref(camera), C.byref(scene), row0, row1, _ptr(rgba), _ptr(stats), _stream_handle(stream)))
+
+    def render_striped_device(self, camera, scene, stripe_rows, rank, ranks, rgba, stats=None, stream=None):
+        _check(self.lib.bz_render_striped(self.h, C.byref(camera), C.byref(scene), stripe_rows, rank, ranks, _ptr(rgba), _ptr(stats),
+                                          _stream_handle(stream)))
+
+
+def generate_rays_device(camera, start, direction, row0=0, row1=None, stream=None):
+    row1 = camera.height if row1 is None else row1
+    _check(load().bz_generate_rays(C.byref(camera), row0, row1, _ptr(start), _ptr(direction), _stream_handle(stream)))

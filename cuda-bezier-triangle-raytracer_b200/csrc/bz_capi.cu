@@ -1,0 +1,430 @@
+// bz_capi.cu -- the C ABI of include/bz_capi.h: lens handles, table upload, kernel launches.
+// No CPU path: every computing entry point needs a CUDA device and fails with BZ_ERR_NO_DEVICE /
+// BZ_ERR_CUDA otherwise.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "bz_capi.h"
+#include "bz_device.h"
+#include "../host/bz_bvh.h"
+
+cudaError_t bz_launch_trace(int job, bool brute, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream);
+cudaError_t bz_launch_resolve(const uint32_t *accum, uint8_t *rgba, uint64_t pixels, uint32_t spp, cudaStream_t stream);
+cudaError_t bz_launch_raygen(const bz_camera &cam, uint32_t row0, uint64_t count, float *start, float *dir, cudaStream_t stream);
+cudaError_t bz_launch_fma_probe(float *sink, uint32_t iters, int grid, cudaStream_t stream);
+int bz_trace_threads(void);
+
+static thread_local std::string gError;
+
+static int bz_fail(int code, const std::string &text) {
+  gError = text;
+  return code;
+}
+
+#define BZ_CUDA(call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) { \
+  return bz_fail(BZ_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while(0)
+
+struct bz_lens {
+  int        device;
+  int        sm_count;
+  uint32_t   mode;
+  bz_tables  tables;
+  float4    *d_cull, *d_newton, *d_leaf, *d_nodes;
+  unsigned long long *d_counter;      // work counter of the persistent kernel
+  uint32_t  *d_accum;                 // render scratch: one u32 per pixel of the largest band so far
+  size_t     accum_pixels;
+  void      *d_scratch;               // *_host staging
+  size_t     scratch_bytes;
+  cudaEvent_t ev_begin, ev_end;
+  cudaStream_t last_stream;
+  bool       timed;
+  uint32_t   bvh_depth;
+};
+
+static int bz_check_device(int device) {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if(e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    return bz_fail(BZ_ERR_NO_DEVICE, "no usable CUDA device (there is no CPU path)");
+  }
+  if(device < 0 || device >= count) { return bz_fail(BZ_ERR_INVALID, "device index out of range"); }
+  return BZ_OK;
+}
+
+extern "C" {
+
+const char *bz_last_error(void) { return gError.c_str(); }
+
+int bz_device_count(int *out_count) {
+  if(out_count == nullptr) { return bz_fail(BZ_ERR_INVALID, "out_count is null"); }
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if(e != cudaSuccess) { cudaGetLastError(); count = 0; }
+  *out_count = count;
+  return BZ_OK;
+}
+
+uint32_t bz_sizeof_patch(void) { return (uint32_t)sizeof(bz_patch); }
+uint32_t bz_sizeof_camera(void) { return (uint32_t)sizeof(bz_camera); }
+uint32_t bz_sizeof_scene(void) { return (uint32_t)sizeof(bz_scene); }
+uint32_t bz_sizeof_stats(void) { return (uint32_t)sizeof(bz_stats); }
+
+int bz_lens_destroy(bz_lens *lens) {
+  if(lens == nullptr) { return BZ_OK; }
+  cudaSetDevice(lens->device);
+  cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_nodes);
+  cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch);
+  if(lens->ev_begin) { cudaEventDestroy(lens->ev_begin); }
+  if(lens->ev_end) { cudaEventDestroy(lens->ev_end); }
+  delete lens;
+  return BZ_OK;
+}
+
+static void bz_pack_cull(const bz_patch &p, uint32_t index, float *out) {
+  out[0] = p.plane[0]; out[1] = p.plane[1]; out[2] = p.plane[2]; out[3] = p.plane[3];
+  out[4] = p.bary_inv[0][0]; out[5] = p.bary_inv[0][1]; out[6] = p.bary_inv[0][2]; out[7] = p.height_inside;
+  out[8] = p.bary_inv[1][0]; out[9] = p.bary_inv[1][1]; out[10] = p.bary_inv[1][2]; out[11] = p.height_outside;
+  out[12] = p.bary_inv[2][0]; out[13] = p.bary_inv[2][1]; out[14] = p.bary_inv[2][2];
+  std::memcpy(out + 15, &index, sizeof(index));
+}
+
+int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refractive_index, int device, bz_lens **out_lens) {
+  if(out_lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "out_lens is null"); }
+  *out_lens = nullptr;
+  if(h_patches == nullptr && patch_count != 0u) { return bz_fail(BZ_ERR_INVALID, "h_patches is null"); }
+  if(patch_count >= (1u << 28)) { return bz_fail(BZ_ERR_INVALID, "too many patches"); }
+  int rc = bz_check_device(device);
+  if(rc != BZ_OK) { return rc; }
+  BZ_CUDA(cudaSetDevice(device));
+
+  bz_bvh bvh;
+  bz_build_bvh(h_patches, patch_count, bvh);
+  if(bvh.depth * 3u + 4u > 64u) { return bz_fail(BZ_ERR_INVALID, "cull hierarchy too deep for the traversal stack"); }
+  std::vector<float> cull((size_t)patch_count * 16u), newton((size_t)patch_count * 48u);
+  for(uint32_t i = 0u; i < patch_count; ++i) {
+    const bz_patch &p = h_patches[i];
+    bz_pack_cull(p, i, cull.data() + (size_t)i * 16u);
+    float *w = newton.data() + (size_t)i * 48u;
+    std::memcpy(w, p.control, 30u * sizeof(float));
+    std::memcpy(w + 30, p.dir_b, 3u * sizeof(float));
+    std::memcpy(w + 33, p.divider, 12u * sizeof(float));
+    std::memcpy(w + 45, p.neighbours, 3u * sizeof(uint32_t));
+  }
+  size_t const slots = bvh.order.size() + bvh.always.size();
+  std::vector<float> leaf(slots * 16u);
+  for(size_t k = 0u; k < bvh.order.size(); ++k) { bz_pack_cull(h_patches[bvh.order[k]], bvh.order[k], leaf.data() + k * 16u); }
+  for(size_t k = 0u; k < bvh.always.size(); ++k) { bz_pack_cull(h_patches[bvh.always[k]], bvh.always[k], leaf.data() + (bvh.order.size() + k) * 16u); }
+
+  bz_lens *lens = new bz_lens();
+  std::memset(lens, 0, sizeof(*lens));
+  lens->device = device;
+  lens->mode = BZ_MODE_CULLED;
+  lens->bvh_depth = bvh.depth;
+  cudaDeviceProp prop;
+  cudaError_t e = cudaGetDeviceProperties(&prop, device);
+  if(e != cudaSuccess) { delete lens; return bz_fail(BZ_ERR_CUDA, cudaGetErrorString(e)); }
+  lens->sm_count = prop.multiProcessorCount;
+  auto upload = [&](const std::vector<float> &src, float4 **dst) -> cudaError_t {
+    size_t bytes = std::max<size_t>(src.size() * sizeof(float), 16u);
+    cudaError_t r = cudaMalloc((void**)dst, bytes);
+    if(r != cudaSuccess) { return r; }
+    if(!src.empty()) { r = cudaMemcpy(*dst, src.data(), src.size() * sizeof(float), cudaMemcpyHostToDevice); }
+    return r;
+  };
+  e = upload(cull, &lens->d_cull);
+  if(e == cudaSuccess) { e = upload(newton, &lens->d_newton); }
+  if(e == cudaSuccess) { e = upload(leaf, &lens->d_leaf); }
+  if(e == cudaSuccess) { e = upload(bvh.nodes, &lens->d_nodes); }
+  if(e == cudaSuccess) { e = cudaMalloc((void**)&lens->d_counter, 64u); }
+  if(e == cudaSuccess) { e = cudaEventCreate(&lens->ev_begin); }
+  if(e == cudaSuccess) { e = cudaEventCreate(&lens->ev_end); }
+  if(e != cudaSuccess) {
+    std::string text = cudaGetErrorString(e);
+    bz_lens_destroy(lens);
+    return bz_fail(BZ_ERR_CUDA, "bz_lens_create: " + text);
+  }
+  lens->tables.cull = lens->d_cull;
+  lens->tables.newton = lens->d_newton;
+  lens->tables.leaf = lens->d_leaf;
+  lens->tables.nodes = lens->d_nodes;
+  lens->tables.patch_count = patch_count;
+  lens->tables.node_count = (uint32_t)(bvh.nodes.size() / 32u);
+  lens->tables.always_first = (uint32_t)bvh.order.size();
+  lens->tables.always_count = (uint32_t)bvh.always.size();
+  lens->tables.ri = refractive_index;
+  lens->tables.extent = bvh.extent;
+  *out_lens = lens;
+  return BZ_OK;
+}
+
+int bz_lens_set_mode(bz_lens *lens, uint32_t mode) {
+  if(lens == nullptr || mode > BZ_MODE_CULLED) { return bz_fail(BZ_ERR_INVALID, "bad lens or mode"); }
+  lens->mode = mode;
+  return BZ_OK;
+}
+
+int bz_lens_patch_count(const bz_lens *lens, uint32_t *out_count) {
+  if(lens == nullptr || out_count == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  *out_count = lens->tables.patch_count;
+  return BZ_OK;
+}
+
+int bz_lens_info(const bz_lens *lens, uint32_t out[4]) {
+  if(lens == nullptr || out == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  out[0] = lens->tables.node_count;
+  out[1] = lens->bvh_depth;
+  out[2] = lens->tables.always_count;
+  out[3] = (uint32_t)lens->sm_count;
+  return BZ_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ launches ----
+
+static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
+  BZ_CUDA(cudaSetDevice(lens->device));
+  lens->timed = false;
+  if(desc.ray_count == 0u) { return BZ_OK; }
+  BZ_CUDA(cudaMemsetAsync(lens->d_counter, 0, sizeof(unsigned long long), stream));
+  desc.next_ray = lens->d_counter;
+  uint64_t const threads = (uint64_t)bz_trace_threads();
+  uint64_t const wanted = (desc.ray_count + threads - 1u) / threads;
+  int const grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * 2u, wanted);
+  BZ_CUDA(cudaEventRecord(lens->ev_begin, stream));
+  BZ_CUDA(bz_launch_trace(job, lens->mode == BZ_MODE_BRUTE, lens->tables, desc, grid, stream));
+  BZ_CUDA(cudaEventRecord(lens->ev_end, stream));
+  lens->last_stream = stream;
+  lens->timed = true;
+  return BZ_OK;
+}
+
+static int bz_scratch(bz_lens *lens, size_t bytes) {
+  if(bytes <= lens->scratch_bytes) { return BZ_OK; }
+  BZ_CUDA(cudaSetDevice(lens->device));
+  if(lens->d_scratch != nullptr) { BZ_CUDA(cudaFree(lens->d_scratch)); lens->d_scratch = nullptr; lens->scratch_bytes = 0u; }
+  BZ_CUDA(cudaMalloc(&lens->d_scratch, bytes));
+  lens->scratch_bytes = bytes;
+  return BZ_OK;
+}
+
+static int bz_render_common(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t rows,
+                            uint32_t stripe_rows, uint32_t rank, uint32_t ranks, uint8_t *d_rgba, bz_stats *d_stats, cudaStream_t stream) {
+  if(camera->width == 0u || camera->height == 0u || camera->strata == 0u) { return bz_fail(BZ_ERR_INVALID, "empty camera"); }
+  if(rows == 0u) { lens->timed = false; return BZ_OK; }
+  if(d_rgba == nullptr) { return bz_fail(BZ_ERR_INVALID, "d_rgba is null"); }
+  BZ_CUDA(cudaSetDevice(lens->device));
+  size_t const pixels = (size_t)rows * camera->width;
+  if(pixels >= (1ull << 32)) { return bz_fail(BZ_ERR_INVALID, "band too large"); }
+  if(pixels > lens->accum_pixels) {
+    if(lens->d_accum != nullptr) { BZ_CUDA(cudaFree(lens->d_accum)); lens->d_accum = nullptr; lens->accum_pixels = 0u; }
+    BZ_CUDA(cudaMalloc((void**)&lens->d_accum, pixels * sizeof(uint32_t)));
+    lens->accum_pixels = pixels;
+  }
+  BZ_CUDA(cudaMemsetAsync(lens->d_accum, 0, pixels * sizeof(uint32_t), stream));
+  bz_job desc;
+  std::memset(&desc, 0, sizeof(desc));
+  desc.camera = *camera;
+  desc.scene = *scene;
+  desc.row0 = row0;
+  desc.stripe_rows = stripe_rows;
+  desc.stripe_rank = rank;
+  desc.stripe_ranks = ranks;
+  desc.accum = lens->d_accum;
+  uint32_t const spp = camera->strata * camera->strata;
+  desc.ray_count = (uint64_t)pixels * spp;
+  desc.stats = (unsigned long long*)d_stats;
+  int rc = bz_run(lens, BZ_JOB_RENDER, desc, stream);
+  if(rc != BZ_OK) { return rc; }
+  BZ_CUDA(bz_launch_resolve(lens->d_accum, d_rgba, pixels, spp, stream));
+  return BZ_OK;
+}
+
+extern "C" {
+
+int bz_refract_batch(bz_lens *lens, const float *d_start, const float *d_dir, const uint32_t *d_expected, uint64_t n,
+                     float *d_out_start, float *d_out_dir, uint32_t *d_out_status, uint32_t *d_out_patch, void *stream) {
+  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+  if(n != 0u && (d_start == nullptr || d_dir == nullptr || d_expected == nullptr || d_out_start == nullptr || d_out_dir == nullptr || d_out_status == nullptr)) {
+    return bz_fail(BZ_ERR_INVALID, "null ray buffer");
+  }
+  bz_job desc;
+  std::memset(&desc, 0, sizeof(desc));
+  desc.in_start = d_start; desc.in_dir = d_dir; desc.in_expected = d_expected;
+  desc.out_start = d_out_start; desc.out_dir = d_out_dir; desc.out_status = d_out_status; desc.out_patch = d_out_patch;
+  desc.ray_count = n;
+  return bz_run(lens, BZ_JOB_REFRACT, desc, (cudaStream_t)stream);
+}
+
+int bz_intersect_batch(bz_lens *lens, const float *d_start, const float *d_dir, uint64_t n,
+                       uint32_t *d_out_what, uint32_t *d_out_patch, float *d_out_distance, float *d_out_point,
+                       float *d_out_normal, float *d_out_cos, float *d_out_bary, void *stream) {
+  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+  if(n != 0u && (d_start == nullptr || d_dir == nullptr || d_out_what == nullptr)) { return bz_fail(BZ_ERR_INVALID, "null ray buffer"); }
+  bz_job desc;
+  std::memset(&desc, 0, sizeof(desc));
+  desc.in_start = d_start; desc.in_dir = d_dir;
+  desc.out_status = d_out_what; desc.out_patch = d_out_patch; desc.out_distance = d_out_distance; desc.out_point = d_out_point;
+  desc.out_normal = d_out_normal; desc.out_cos = d_out_cos; desc.out_bary = d_out_bary;
+  desc.ray_count = n;
+  return bz_run(lens, BZ_JOB_INTERSECT, desc, (cudaStream_t)stream);
+}
+
+int bz_refract_batch_host(bz_lens *lens, const float *h_start, const float *h_dir, const uint32_t *h_expected, uint64_t n,
+                          float *h_out_start, float *h_out_dir, uint32_t *h_out_status, uint32_t *h_out_patch) {
+  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+  if(n == 0u) { return BZ_OK; }
+  if(h_start == nullptr || h_dir == nullptr || h_expected == nullptr || h_out_start == nullptr || h_out_dir == nullptr || h_out_status == nullptr) {
+    return bz_fail(BZ_ERR_INVALID, "null ray buffer");
+  }
+  int rc = bz_scratch(lens, (size_t)n * 60u);
+  if(rc != BZ_OK) { return rc; }
+  float *ds = (float*)lens->d_scratch, *dd = ds + n * 3u, *os = dd + n * 3u, *od = os + n * 3u;
+  uint32_t *de = (uint32_t*)(od + n * 3u), *ost = de + n, *op = ost + n;
+  BZ_CUDA(cudaMemcpyAsync(ds, h_start, n * 12u, cudaMemcpyHostToDevice, 0));
+  BZ_CUDA(cudaMemcpyAsync(dd, h_dir, n * 12u, cudaMemcpyHostToDevice, 0));
+  BZ_CUDA(cudaMemcpyAsync(de, h_expected, n * 4u, cudaMemcpyHostToDevice, 0));
+  rc = bz_refract_batch(lens, ds, dd, de, n, os, od, ost, op, nullptr);
+  if(rc != BZ_OK) { return rc; }
+  BZ_CUDA(cudaMemcpyAsync(h_out_start, os, n * 12u, cudaMemcpyDeviceToHost, 0));
+  BZ_CUDA(cudaMemcpyAsync(h_out_dir, od, n * 12u, cudaMemcpyDeviceToHost, 0));
+  BZ_CUDA(cudaMemcpyAsync(h_out_status, ost, n * 4u, cudaMemcpyDeviceToHost, 0));
+  if(h_out_patch != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_patch, op, n * 4u, cudaMemcpyDeviceToHost, 0)); }
+  BZ_CUDA(cudaStreamSynchronize(0));
+  return BZ_OK;
+}
+
+int bz_intersect_batch_host(bz_lens *lens, const float *h_start, const float *h_dir, uint64_t n,
+                            uint32_t *h_out_what, uint32_t *h_out_patch, float *h_out_distance, float *h_out_point,
+                            float *h_out_normal, float *h_out_cos, float *h_out_bary) {
+  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+  if(n == 0u) { return BZ_OK; }
+  if(h_start == nullptr || h_dir == nullptr || h_out_what == nullptr) { return bz_fail(BZ_ERR_INVALID, "null ray buffer"); }
+  int rc = bz_scratch(lens, (size_t)n * 76u);
+  if(rc != BZ_OK) { return rc; }
+  float *ds = (float*)lens->d_scratch, *dd = ds + n * 3u, *opt = dd + n * 3u, *onr = opt + n * 3u, *oba = onr + n * 3u;
+  float *odi = oba + n * 3u, *oco = odi + n;
+  uint32_t *owh = (uint32_t*)(oco + n), *opa = owh + n;
+  BZ_CUDA(cudaMemcpyAsync(ds, h_start, n * 12u, cudaMemcpyHostToDevice, 0));
+  BZ_CUDA(cudaMemcpyAsync(dd, h_dir, n * 12u, cudaMemcpyHostToDevice, 0));
+  rc = bz_intersect_batch(lens, ds, dd, n, owh, opa, odi, opt, onr, oco, oba, nullptr);
+  if(rc != BZ_OK) { return rc; }
+  BZ_CUDA(cudaMemcpyAsync(h_out_what, owh, n * 4u, cudaMemcpyDeviceToHost, 0));
+  if(h_out_patch != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_patch, opa, n * 4u, cudaMemcpyDeviceToHost, 0)); }
+  if(h_out_distance != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_distance, odi, n * 4u, cudaMemcpyDeviceToHost, 0)); }
+  if(h_out_cos != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_cos, oco, n * 4u, cudaMemcpyDeviceToHost, 0)); }
+  if(h_out_point != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_point, opt, n * 12u, cudaMemcpyDeviceToHost, 0)); }
+  if(h_out_normal != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_normal, onr, n * 12u, cudaMemcpyDeviceToHost, 0)); }
+  if(h_out_bary != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_bary, oba, n * 12u, cudaMemcpyDeviceToHost, 0)); }
+  BZ_CUDA(cudaStreamSynchronize(0));
+  return BZ_OK;
+}
+
+int bz_generate_rays(const bz_camera *camera, uint32_t row0, uint32_t row1, float *d_start, float *d_dir, void *stream) {
+  if(camera == nullptr || row1 < row0 || row1 > camera->height) { return bz_fail(BZ_ERR_INVALID, "bad camera or rows"); }
+  uint64_t const count = (uint64_t)(row1 - row0) * camera->width * camera->strata * camera->strata;
+  if(count != 0u && (d_start == nullptr || d_dir == nullptr)) { return bz_fail(BZ_ERR_INVALID, "null ray buffer"); }
+  int devices = 0;
+  if(cudaGetDeviceCount(&devices) != cudaSuccess || devices == 0) { cudaGetLastError(); return bz_fail(BZ_ERR_NO_DEVICE, "no usable CUDA device (there is no CPU path)"); }
+  BZ_CUDA(bz_launch_raygen(*camera, row0, count, d_start, d_dir, (cudaStream_t)stream));
+  return BZ_OK;
+}
+
+int bz_render(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
+              uint8_t *d_rgba, bz_stats *d_stats, void *stream) {
+  if(lens == nullptr || camera == nullptr || scene == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  if(row1 < row0 || row1 > camera->height) { return bz_fail(BZ_ERR_INVALID, "bad rows"); }
+  return bz_render_common(lens, camera, scene, row0, row1 - row0, 0u, 0u, 1u, d_rgba, d_stats, (cudaStream_t)stream);
+}
+
+uint32_t bz_striped_rows(uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t ranks) {
+  if(stripe_rows == 0u || ranks == 0u || rank >= ranks) { return 0u; }
+  uint32_t rows = 0u;
+  for(uint32_t first = rank * stripe_rows; first < height; first += ranks * stripe_rows) { rows += std::min(stripe_rows, height - first); }
+  return rows;
+}
+
+int bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t stripe_rows, uint32_t rank,
+                      uint32_t ranks, uint8_t *d_rgba, bz_stats *d_stats, void *stream) {
+  if(lens == nullptr || camera == nullptr || scene == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  if(stripe_rows == 0u || ranks == 0u || rank >= ranks) { return bz_fail(BZ_ERR_INVALID, "bad stripe layout"); }
+  uint32_t const rows = bz_striped_rows(camera->height, stripe_rows, rank, ranks);
+  return bz_render_common(lens, camera, scene, 0u, rows, stripe_rows, rank, ranks, d_rgba, d_stats, (cudaStream_t)stream);
+}
+
+int bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
+                   uint8_t *h_rgba, bz_stats *h_stats) {
+  if(lens == nullptr || camera == nullptr || scene == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  if(row1 < row0 || row1 > camera->height) { return bz_fail(BZ_ERR_INVALID, "bad rows"); }
+  size_t const bytes = (size_t)(row1 - row0) * camera->width * 4u;
+  if(bytes == 0u) { return BZ_OK; }
+  if(h_rgba == nullptr) { return bz_fail(BZ_ERR_INVALID, "h_rgba is null"); }
+  int rc = bz_scratch(lens, bytes + 128u);
+  if(rc != BZ_OK) { return rc; }
+  bz_stats *d_stats = (bz_stats*)lens->d_scratch;
+  uint8_t *d_rgba = (uint8_t*)lens->d_scratch + 128u;
+  BZ_CUDA(cudaMemsetAsync(d_stats, 0, sizeof(bz_stats), 0));
+  rc = bz_render(lens, camera, scene, row0, row1, d_rgba, h_stats != nullptr ? d_stats : nullptr, nullptr);
+  if(rc != BZ_OK) { return rc; }
+  BZ_CUDA(cudaMemcpyAsync(h_rgba, d_rgba, bytes, cudaMemcpyDeviceToHost, 0));
+  if(h_stats != nullptr) {
+    bz_stats fresh;
+    BZ_CUDA(cudaMemcpyAsync(&fresh, d_stats, sizeof(bz_stats), cudaMemcpyDeviceToHost, 0));
+    BZ_CUDA(cudaStreamSynchronize(0));
+    uint64_t *acc = (uint64_t*)h_stats;
+    const uint64_t *add = (const uint64_t*)&fresh;
+    for(size_t i = 0u; i < sizeof(bz_stats) / sizeof(uint64_t); ++i) { acc[i] += add[i]; }
+  }
+  BZ_CUDA(cudaStreamSynchronize(0));
+  return BZ_OK;
+}
+
+int bz_last_kernel_ms(bz_lens *lens, float *out_ms) {
+  if(lens == nullptr || out_ms == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  *out_ms = 0.0f;
+  if(!lens->timed) { return BZ_OK; }
+  BZ_CUDA(cudaSetDevice(lens->device));
+  BZ_CUDA(cudaEventSynchronize(lens->ev_end));
+  BZ_CUDA(cudaEventElapsedTime(out_ms, lens->ev_begin, lens->ev_end));
+  return BZ_OK;
+}
+
+int bz_fp32_peak_probe(int device, float *out_tflops, float *out_ms) {
+  if(out_tflops == nullptr) { return bz_fail(BZ_ERR_INVALID, "out_tflops is null"); }
+  int rc = bz_check_device(device);
+  if(rc != BZ_OK) { return rc; }
+  BZ_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  BZ_CUDA(cudaGetDeviceProperties(&prop, device));
+  float *sink = nullptr;
+  BZ_CUDA(cudaMalloc((void**)&sink, 16u));
+  cudaEvent_t a, b;
+  BZ_CUDA(cudaEventCreate(&a));
+  BZ_CUDA(cudaEventCreate(&b));
+  int const grid = prop.multiProcessorCount * 8;
+  uint32_t const iters = 1u << 16;
+  float best = 1e30f;
+  for(int rep = 0; rep < 4; ++rep) {
+    BZ_CUDA(cudaEventRecord(a, 0));
+    BZ_CUDA(bz_launch_fma_probe(sink, iters, grid, 0));
+    BZ_CUDA(cudaEventRecord(b, 0));
+    BZ_CUDA(cudaEventSynchronize(b));
+    float ms = 0.0f;
+    BZ_CUDA(cudaEventElapsedTime(&ms, a, b));
+    if(rep > 0) { best = std::min(best, ms); }
+  }
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  cudaFree(sink);
+  double const flop = 2.0 * 8.0 * (double)iters * 256.0 * (double)grid;
+  *out_tflops = (float)(flop / ((double)best * 1e-3) * 1e-12);
+  if(out_ms != nullptr) { *out_ms = best; }
+  return BZ_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,242 @@
+// bz_bvh.cpp -- host-side build of the exact cull hierarchy used by BZ_MODE_CULLED.
+//
+// The reference tests every patch for every ray (bezierMesh.cpp:207 "Brute-force for now"); a patch
+// reaches the root search only if the ray meets its FLAT underlying triangle (control points 0, 1, 2)
+// in front of the start (bezierTriangle.cpp:124-131).  A 4-wide bounding-volume hierarchy over the
+// axis-aligned boxes of those flat triangles therefore preserves the candidate set exactly, provided
+// the box test is conservative with respect to the FP32 rounding of stage A.  That slack is applied
+// per ray in the kernel (it depends on the ray's origin); here the only per-patch input is the
+// conditioning kappa = max_i |row_i(Binv)|_1 * altitude_i, which scales the barycentric rounding
+// error into a distance.  Patches with kappa > 16 (underlying plane passing close to the origin, or
+// a degenerate inverse) are not put into the hierarchy at all: they go to the "always" segment and
+// are tested for every ray, as the reference does.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <vector>
+#include "bz_bvh.h"
+
+namespace {
+
+struct Box {
+  float lo[3], hi[3];
+  void reset() { for(int k = 0; k < 3; ++k) { lo[k] = std::numeric_limits<float>::max(); hi[k] = -std::numeric_limits<float>::max(); } }
+  void grow(const float *p) { for(int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], p[k]); hi[k] = std::max(hi[k], p[k]); } }
+  void grow(const Box &b) { for(int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], b.lo[k]); hi[k] = std::max(hi[k], b.hi[k]); } }
+  double area() const {
+    double dx = double(hi[0]) - lo[0], dy = double(hi[1]) - lo[1], dz = double(hi[2]) - lo[2];
+    if(dx < 0.0 || dy < 0.0 || dz < 0.0) { return 0.0; }
+    return 2.0 * (dx * dy + dy * dz + dz * dx);
+  }
+};
+
+struct Binary {
+  Box box;
+  int left, right;          // -1 for leaves
+  uint32_t first, count;    // leaf range in `order`
+};
+
+constexpr int cBins = 16;
+constexpr double cKappaLimit = 16.0;
+
+struct Builder {
+  std::vector<Box> boxes;            // per primitive (index into prims)
+  std::vector<float> centroid;       // 3 per primitive
+  std::vector<uint32_t> order;       // permutation being partitioned
+  std::vector<Binary> nodes;
+
+  int build(uint32_t begin, uint32_t end, int depth) {
+    Binary node;
+    node.box.reset();
+    Box cbox;
+    cbox.reset();
+    for(uint32_t i = begin; i < end; ++i) {
+      node.box.grow(boxes[order[i]]);
+      cbox.grow(&centroid[3u * order[i]]);
+    }
+    node.left = node.right = -1;
+    node.first = begin;
+    node.count = end - begin;
+    int const index = static_cast<int>(nodes.size());
+    nodes.push_back(node);
+    if(end - begin <= 3u) { return index; }
+
+    uint32_t mid = begin;
+    bool split = false;
+    if(depth < 40) {
+      double best = std::numeric_limits<double>::max();
+      int bestAxis = -1, bestBin = -1;
+      for(int axis = 0; axis < 3; ++axis) {
+        double const lo = cbox.lo[axis], extent = double(cbox.hi[axis]) - lo;
+        if(!(extent > 0.0)) { continue; }
+        Box bin[cBins];
+        uint32_t cnt[cBins] = {};
+        for(auto &b : bin) { b.reset(); }
+        for(uint32_t i = begin; i < end; ++i) {
+          int k = std::min(cBins - 1, static_cast<int>((centroid[3u * order[i] + axis] - lo) / extent * cBins));
+          bin[k].grow(boxes[order[i]]);
+          ++cnt[k];
+        }
+        double rightArea[cBins];
+        Box acc;
+        acc.reset();
+        uint32_t n = 0u;
+        uint32_t rightCount[cBins];
+        for(int k = cBins - 1; k > 0; --k) {
+          acc.grow(bin[k]);
+          n += cnt[k];
+          rightArea[k] = acc.area();
+          rightCount[k] = n;
+        }
+        acc.reset();
+        n = 0u;
+        for(int k = 0; k < cBins - 1; ++k) {
+          acc.grow(bin[k]);
+          n += cnt[k];
+          if(n == 0u || rightCount[k + 1] == 0u) { continue; }
+          double cost = acc.area() * n + rightArea[k + 1] * rightCount[k + 1];
+          if(cost < best) { best = cost; bestAxis = axis; bestBin = k; }
+        }
+      }
+      if(bestAxis >= 0) {
+        double const lo = cbox.lo[bestAxis], extent = double(cbox.hi[bestAxis]) - lo;
+        auto middle = std::partition(order.begin() + begin, order.begin() + end, [&](uint32_t p) {
+          int k = std::min(cBins - 1, static_cast<int>((centroid[3u * p + bestAxis] - lo) / extent * cBins));
+          return k <= bestBin;
+        });
+        mid = static_cast<uint32_t>(middle - order.begin());
+        split = (mid > begin && mid < end);
+      }
+    }
+    if(!split) {
+      mid = begin + (end - begin) / 2u;   // coincident centroids or depth cap: split the index range
+    }
+    int const left = build(begin, mid, depth + 1);
+    int const right = build(mid, end, depth + 1);
+    nodes[index].left = left;
+    nodes[index].right = right;
+    nodes[index].count = 0u;
+    return index;
+  }
+};
+
+void writeChild(std::vector<float> &out, size_t node, int slot, const Box &box, int32_t code) {
+  float *p = out.data() + node * 32u;
+  p[0 + slot] = box.lo[0];  p[4 + slot] = box.hi[0];
+  p[8 + slot] = box.lo[1];  p[12 + slot] = box.hi[1];
+  p[16 + slot] = box.lo[2]; p[20 + slot] = box.hi[2];
+  static_assert(sizeof(float) == sizeof(int32_t), "child codes are stored in float lanes");
+  std::memcpy(p + 24 + slot, &code, sizeof(code));
+}
+
+}
+
+
+
+void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out) {
+  out.nodes.clear();
+  out.order.clear();
+  out.always.clear();
+  out.extent = 0.0f;
+  out.depth = 0u;
+  Builder b;
+  std::vector<uint32_t> prims;     // primitive -> patch
+  for(uint32_t i = 0u; i < count; ++i) {
+    const bz_patch &p = patches[i];
+    const float *v[3] = { p.control[0], p.control[1], p.control[2] };
+    bool finite = true;
+    for(int a = 0; a < 3; ++a) {
+      for(int k = 0; k < 3; ++k) { finite = finite && std::isfinite(v[a][k]); }
+    }
+    double kappa = std::numeric_limits<double>::infinity();
+    if(finite) {
+      double e[3][3];   // e[i] = edge opposite vertex i
+      for(int k = 0; k < 3; ++k) {
+        e[0][k] = double(v[2][k]) - v[1][k];
+        e[1][k] = double(v[0][k]) - v[2][k];
+        e[2][k] = double(v[1][k]) - v[0][k];
+      }
+      double cx = e[2][1] * -e[1][2] - e[2][2] * -e[1][1];
+      double cy = e[2][2] * -e[1][0] - e[2][0] * -e[1][2];
+      double cz = e[2][0] * -e[1][1] - e[2][1] * -e[1][0];
+      double const twiceArea = std::sqrt(cx * cx + cy * cy + cz * cz);
+      kappa = 0.0;
+      for(int i3 = 0; i3 < 3; ++i3) {
+        double const edge = std::sqrt(e[i3][0] * e[i3][0] + e[i3][1] * e[i3][1] + e[i3][2] * e[i3][2]);
+        double const altitude = twiceArea / edge;
+        double const row = std::fabs(double(p.bary_inv[i3][0])) + std::fabs(double(p.bary_inv[i3][1])) + std::fabs(double(p.bary_inv[i3][2]));
+        kappa = std::max(kappa, row * altitude);
+        if(!(row * altitude == row * altitude)) { kappa = std::numeric_limits<double>::infinity(); }
+      }
+      for(int a = 0; a < 3; ++a) {
+        for(int k = 0; k < 3; ++k) { out.extent = std::max(out.extent, std::fabs(v[a][k])); }
+      }
+    }
+    if(!(kappa <= cKappaLimit)) {
+      out.always.push_back(i);
+      continue;
+    }
+    Box box;
+    box.reset();
+    for(int a = 0; a < 3; ++a) { box.grow(v[a]); }
+    b.boxes.push_back(box);
+    for(int k = 0; k < 3; ++k) { b.centroid.push_back((v[0][k] + v[1][k] + v[2][k]) / 3.0f); }
+    prims.push_back(i);
+  }
+  uint32_t const n = static_cast<uint32_t>(prims.size());
+  if(n == 0u) { return; }
+  b.order.resize(n);
+  for(uint32_t i = 0u; i < n; ++i) { b.order[i] = i; }
+  b.nodes.reserve(2u * n);
+  int const root = b.build(0u, n, 0);
+  out.order.resize(n);
+  for(uint32_t i = 0u; i < n; ++i) { out.order[i] = prims[b.order[i]]; }
+
+  // collapse the binary tree into 4-wide nodes: repeatedly open the inner child with the largest box
+  struct Pending { int binary; size_t wide; uint32_t depth; };
+  std::vector<Pending> todo;
+  auto emit = [&](int binary, uint32_t depth) -> size_t {
+    size_t const at = out.nodes.size() / 32u;
+    out.nodes.resize(out.nodes.size() + 32u, 0.0f);
+    todo.push_back({ binary, at, depth });
+    return at;
+  };
+  emit(root, 1u);
+  while(!todo.empty()) {
+    Pending const job = todo.back();
+    todo.pop_back();
+    out.depth = std::max(out.depth, job.depth);
+    std::vector<int> kids;
+    if(b.nodes[job.binary].left < 0) {
+      kids.push_back(job.binary);           // the whole tree is one leaf
+    }
+    else {
+      kids.push_back(b.nodes[job.binary].left);
+      kids.push_back(b.nodes[job.binary].right);
+      while(kids.size() < 4u) {
+        int pick = -1;
+        double area = -1.0;
+        for(size_t k = 0u; k < kids.size(); ++k) {
+          if(b.nodes[kids[k]].left >= 0 && b.nodes[kids[k]].box.area() > area) { area = b.nodes[kids[k]].box.area(); pick = static_cast<int>(k); }
+        }
+        if(pick < 0) { break; }
+        int const opened = kids[pick];
+        kids[pick] = b.nodes[opened].left;
+        kids.push_back(b.nodes[opened].right);
+      }
+    }
+    for(size_t k = 0u; k < kids.size(); ++k) {
+      Binary const &kid = b.nodes[kids[k]];
+      int32_t code;
+      if(kid.left < 0) {
+        code = ~static_cast<int32_t>((kid.first << 3u) | kid.count);
+      }
+      else {
+        code = static_cast<int32_t>(emit(kids[k], job.depth + 1u));
+      }
+      writeChild(out.nodes, job.wide, static_cast<int>(k), kid.box, code);
+    }
+  }
+}

@@ -1,0 +1,19 @@
+// bz_bvh.h -- exact cull hierarchy over the flat underlying triangles of the patches (host build).
+#ifndef BZ_BVH_H
+#define BZ_BVH_H
+
+#include <cstdint>
+#include <vector>
+#include "bz_capi.h"
+
+struct bz_bvh {
+  std::vector<float>    nodes;    // 32 floats per 4-wide node, layout in csrc/bz_device.h
+  std::vector<uint32_t> order;    // leaf slot -> patch index
+  std::vector<uint32_t> always;   // patches outside the hierarchy, tested for every ray
+  float                 extent;   // max |coordinate| of the flat triangles
+  uint32_t              depth;    // levels of 4-wide nodes
+};
+
+void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out);
+
+#endif

@@ -151,6 +151,21 @@ int  bz_render(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, ui
 int  bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
                     uint8_t *h_rgba, bz_stats *h_stats);
 
+/* Row bands for N GPUs (north_star subsystem 4): the image is cut into stripes of `stripe_rows` rows
+ * dealt round-robin to `ranks` ranks; rank r renders stripes r, r+ranks, ... into a compact local
+ * buffer (its rows in image order).  bz_striped_rows gives that buffer's row count. */
+uint32_t bz_striped_rows(uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t ranks);
+int  bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t stripe_rows, uint32_t rank,
+                       uint32_t ranks, uint8_t *d_rgba, bz_stats *d_stats, void *stream);
+
+/* Cull-hierarchy facts of a lens: out[0] = 4-wide nodes, out[1] = levels, out[2] = patches in the
+ * always-tested segment, out[3] = SM count of the device. */
+int  bz_lens_info(const bz_lens *lens, uint32_t out[4]);
+
+/* Measured FP32 issue rate of `device` (dependent-FMA chains, 2 flop per lane and instruction), in
+ * TFLOP/s: the denominator of the FP32 roofline fraction. */
+int  bz_fp32_peak_probe(int device, float *out_tflops, float *out_ms);
+
 /* Device time (ms) of the intersect/refract kernels of the most recent bz_render / bz_refract_batch
  * on this lens, measured with CUDA events on the stream the call used; synchronises that stream. */
 int  bz_last_kernel_ms(bz_lens *lens, float *out_ms);

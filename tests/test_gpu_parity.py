@@ -1,0 +1,154 @@
+"""`-m gpu` parity tests: the CUDA path through the C ABI against the oracle.
+
+Tolerance: the kernels are built with -fmad=false and IEEE div/sqrt, so every comparison with the
+oracle (oracle/_ref = the compiled reference + the documented hoist, and oracle/bz_oracle.c) is
+BIT-EXACT -- stricter than north_star's 1e-5 relative / 1 LSB, which is what a future FMA build
+would be held to.
+"""
+import numpy as np
+import pytest
+
+import common
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = ["sphere16x8", "sphere32x16", "ellipsoid64x32", "robot"]
+RI = {"robot": 1.5}
+
+
+@pytest.fixture(scope="module")
+def bz():
+    import bezier_b200
+    assert bezier_b200.device_count() > 0, "no CUDA device: the product has no CPU path"
+    return bezier_b200
+
+
+@pytest.mark.parametrize("name", CONFIGS)
+@pytest.mark.parametrize("mode", ["brute", "culled"])
+def test_intersect_batch_bit_exact(bz, oracle_built, name, mode):
+    import bzoracle
+    mesh, bezier, patches = common.ref_config(name)
+    lo, hi = common.bbox(mesh)
+    s, d = common.random_rays(lo, hi, 20000, seed=7)
+    ref = bzoracle.intersect(patches, s, d, threads=8)
+    lens = bz.BezierLens(RI.get(name, 1.3), patches).set_mode(bz.MODE_BRUTE if mode == "brute" else bz.MODE_CULLED)
+    got = lens.intersect(s, d)
+    assert int((ref["what"] == 4).sum()) > 1000
+    common.assert_same_hits(ref, got, "%s/%s" % (name, mode))
+
+
+@pytest.mark.parametrize("name", CONFIGS)
+def test_refract_two_crossings_bit_exact_vs_reference(bz, oracle_built, name):
+    """entry + exit refraction through the REAL reference classes (oracle/_ref)"""
+    import bzref
+    mesh, bezier, patches = common.ref_config(name)
+    ri = RI.get(name, 1.3)
+    ref_lens = bzref.RefLens(ri, bezier)
+    lens = bz.BezierLens(ri, patches)
+    lo, hi = common.bbox(mesh)
+    s, d = common.random_rays(lo, hi, 8000, seed=11, inside_fraction=0.0)
+    expected = np.full(s.shape[0], 1, np.uint32)
+    for crossing in range(2):
+        rs, rd, rst = ref_lens.refract(s, d, expected, threads=8)
+        gs, gd, gst, gpatch = lens.refract(s, d, expected)
+        assert np.array_equal(rst, gst), "status differs on %d rays" % int((rst != gst).sum())
+        assert np.array_equal(rs, gs) and np.array_equal(rd, gd)
+        assert int((rst != 0).sum()) > 500
+        s, d = rs, rd
+        expected = np.where(rst == 0, 0, 3 - expected).astype(np.uint32)   # dead rays expect cNone: they stay dead
+
+
+def test_refract_edge_cases(bz, oracle_built):
+    mesh, bezier, patches = common.ref_config("sphere16x8")
+    lens = bz.BezierLens(1.3, patches)
+    # empty batch
+    gs, gd, gst, gp = lens.refract(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.float32), np.zeros(0, np.uint32))
+    assert gs.shape == (0, 3) and gst.shape == (0,)
+    # a single ray, a ragged count (not a multiple of the pool size), rays that miss, wrong expected side
+    s = np.array([[-10, 0.1, 0.2], [-10, 5.0, 5.0], [-10, 0.1, 0.2]], np.float32)
+    d = np.array([[1, 0, 0], [1, 0, 0], [1, 0, 0]], np.float32)
+    gs, gd, gst, gp = lens.refract(s, d, np.array([1, 1, 2], np.uint32))
+    assert list(gst) == [1, 0, 0]
+    assert gp[0] == 350 and gp[1] == bz.NO_PATCH and gp[2] == 350      # SURVEY.md section 4 anchor: entry patch 350
+    assert np.array_equal(gs[1], s[1]) and np.array_equal(gd[2], d[2])   # cNone leaves the ray as it came
+    # empty lens: every ray passes untouched
+    empty = bz.BezierLens(1.3, np.zeros((0, 64), np.float32))
+    gs, gd, gst, gp = empty.refract(s, d, 1)
+    assert list(gst) == [0, 0, 0]
+
+
+@pytest.mark.parametrize("name,w,h,strata,crossings", [("sphere16x8", 160, 120, 1, 2), ("sphere16x8", 64, 48, 4, 2), ("robot", 96, 64, 2, 8)])
+def test_render_pixel_exact_vs_reference(bz, oracle_built, name, w, h, strata, crossings):
+    import bzref
+    mesh, bezier, patches = common.ref_config(name)
+    ri = RI.get(name, 1.3)
+    lo, hi = common.bbox(mesh)
+    half = float(max(hi[1] - lo[1], hi[2] - lo[2])) * 0.5 / 0.6 / (12.0 + float(lo[0]))
+    eye = (float(lo[0]) - 12.0, float(lo[1] + hi[1]) / 2, float(lo[2] + hi[2]) / 2)
+    cam_args = dict(strata=strata, eye=eye, half_w=half)
+    rcam, rscene = bzref.make_camera(w, h, **cam_args), bzref.make_scene(bg_x=float(hi[0]) + 12.0, max_crossings=crossings)
+    ref_rgba, ref_stats, rays = bzref.RefLens(ri, bezier).render(rcam, rscene, threads=8)
+    cam, scene = bz.make_camera(w, h, **cam_args), bz.make_scene(bg_x=float(hi[0]) + 12.0, max_crossings=crossings)
+    for mode in (bz.MODE_CULLED, bz.MODE_BRUTE):
+        rgba, stats = bz.BezierLens(ri, patches).set_mode(mode).render(cam, scene)
+        assert np.array_equal(rgba, ref_rgba), "%d of %d pixels differ" % (int((rgba != ref_rgba).any(-1).sum()), w * h)
+        got, want = stats.as_dict(), ref_stats.as_dict()
+        for key in ("primary_rays", "refract_calls", "entered", "exited", "lost"):
+            assert got[key] == want[key], key
+    assert ref_stats.entered > 100
+
+
+def test_render_bands_and_stripes_compose(bz, oracle_built):
+    """row bands and round-robin stripes reproduce the full frame byte for byte (multi-GPU sharding, one device)"""
+    import torch
+    mesh, bezier, patches = common.ref_config("sphere16x8")
+    lens = bz.BezierLens(1.3, patches)
+    cam, scene = bz.make_camera(96, 70, strata=2, eye=(-12.0, 0.0, 0.0), half_w=0.14), bz.make_scene()
+    full, _ = lens.render(cam, scene)
+    top, _ = lens.render(cam, scene, 0, 33)
+    bottom, _ = lens.render(cam, scene, 33, 70)
+    assert np.array_equal(np.concatenate([top, bottom]), full)
+    ranks, stripe = 4, 8
+    image = np.zeros_like(full)
+    for rank in range(ranks):
+        rows = bz.striped_rows(cam.height, stripe, rank, ranks)
+        buf = torch.zeros((rows, cam.width, 4), dtype=torch.uint8, device="cuda")
+        lens.render_striped_device(cam, scene, stripe, rank, ranks, buf)
+        torch.cuda.synchronize()
+        local = buf.cpu().numpy()
+        r = 0
+        for first in range(rank * stripe, cam.height, ranks * stripe):
+            k = min(stripe, cam.height - first)
+            image[first:first + k] = local[r:r + k]
+            r += k
+        assert r == rows
+    assert np.array_equal(image, full)
+
+
+def test_generate_rays_bit_exact(bz, oracle_built):
+    import bzref
+    import torch
+    for ortho in (False, True):
+        args = dict(strata=3, eye=(-12.0, 0.25, -0.5), half_w=0.2, ortho=ortho)
+        cam, rcam = bz.make_camera(50, 30, **args), bzref.make_camera(50, 30, **args)
+        rs, rd = bzref.generate_rays(rcam, 5, 22)
+        s = torch.zeros(rs.shape, dtype=torch.float32, device="cuda")
+        d = torch.zeros_like(s)
+        bz.generate_rays_device(cam, s, d, 5, 22)
+        torch.cuda.synchronize()
+        assert np.array_equal(s.cpu().numpy(), rs) and np.array_equal(d.cpu().numpy(), rd)
+
+
+def test_queue_overflow_falls_back_inline(bz, oracle_built):
+    """many rays through the same few patches: the candidate queues overflow and the inline path must give the same bits"""
+    import bzoracle
+    mesh, bezier, patches = common.ref_config("sphere16x8")
+    rng = np.random.default_rng(3)
+    n = 50000
+    s = np.zeros((n, 3), np.float32)
+    s[:, 0] = -10
+    s[:, 1:] = (rng.random((n, 2)) * 1.6 - 0.8).astype(np.float32)
+    d = np.tile(np.array([[1, 0, 0]], np.float32), (n, 1))
+    ref = bzoracle.intersect(patches, s, d, threads=8)
+    got = bz.BezierLens(1.3, patches).intersect(s, d)
+    common.assert_same_hits(ref, got, "dense")
