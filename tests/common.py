@@ -79,6 +79,17 @@ def shim_intersect(lib, patches, start, direction, mode):
     return dict(what=what, patch=patch, distance=dist, point=pt, normal=nr, cos=cos, bary=ba), vis
 
 
+def same_bits(a, b):
+    """element-wise equality where NaN matches NaN: the reference accepts a hit whose 4th-iteration surface point is
+    NaN (`NaN > 0.01` is false at bezierTriangle.cpp:165), and x86 and the GPU give NaNs different payload bits"""
+    a, b = np.asarray(a), np.asarray(b)
+    if a.shape != b.shape:
+        return False
+    if a.dtype.kind == "f":
+        return bool(np.all((a == b) | (np.isnan(a) & np.isnan(b))))
+    return bool(np.array_equal(a, b))
+
+
 def assert_same_hits(a, b, label):
     for k in ("what", "patch", "distance", "point", "normal", "cos", "bary"):
-        assert np.array_equal(a[k], b[k]), "%s: %s differs on %d rays" % (label, k, int((a[k] != b[k]).sum()))
+        assert same_bits(a[k], b[k]), "%s: %s differs on %d rays" % (label, k, int((a[k] != b[k]).sum()))
