@@ -103,6 +103,31 @@ SIGNATURES = {
     "bz_striped_rows": (_u32, [_u32, _u32, _u32, _u32]),
     "bz_render_striped": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _u32, _vp, _vp, _vp]),
     "bz_fp32_peak_probe": (_int, [_int, C.POINTER(_f), C.POINTER(_f)]),
+    "bz_mesh_create": (_int, [C.POINTER(_vp)]),
+    "bz_mesh_destroy": (_int, [_vp]),
+    "bz_mesh_clone": (_int, [_vp, C.POINTER(_vp)]),
+    "bz_mesh_make_ellipsoid": (_int, [_vp, _i32, _i32, C.POINTER(_f * 3)]),
+    "bz_mesh_make_unit_sphere": (_int, [_vp, _i32, _i32]),
+    "bz_mesh_read_stl": (_int, [_vp, C.c_char_p]),
+    "bz_mesh_write_stl": (_int, [_vp, C.c_char_p]),
+    "bz_mesh_set_triangles": (_int, [_vp, _vp, _u32]),
+    "bz_mesh_size": (_int, [_vp, C.POINTER(_u32)]),
+    "bz_mesh_get_triangles": (_int, [_vp, _vp]),
+    "bz_mesh_transform": (_int, [_vp, _vp, _vp]),
+    "bz_mesh_split_triangles": (_int, [_vp, _i32]),
+    "bz_mesh_split_triangles_by_side": (_int, [_vp, _f]),
+    "bz_mesh_standardize_vertices": (_int, [_vp]),
+    "bz_mesh_standardize_normals": (_int, [_vp]),
+    "bz_mesh_neighbour_count": (_int, [_vp, C.POINTER(_u32)]),
+    "bz_mesh_get_face2neighbours": (_int, [_vp, _vp, _vp]),
+    "bz_mesh_get_corner_normals": (_int, [_vp, _vp]),
+    "bz_bezier_create": (_int, [_vp, C.POINTER(_vp)]),
+    "bz_bezier_destroy": (_int, [_vp]),
+    "bz_bezier_size": (_int, [_vp, C.POINTER(_u32)]),
+    "bz_bezier_get_patches": (_int, [_vp, _vp]),
+    "bz_bezier_interpolate": (_int, [_vp, _i32, C.POINTER(_vp)]),
+    "bz_bezier_split_thick": (_int, [_vp, C.POINTER(_vp)]),
+    "bz_lens_create_from_bezier": (_int, [_vp, _f, _int, C.POINTER(_vp)]),
     "bz_last_kernel_ms": (_int, [_vp, C.POINTER(_f)]),
 }
 
@@ -161,6 +186,134 @@ def _stream_handle(stream):
     return C.c_void_p(int(stream))
 
 
+class Mesh:
+    """Mesh -- reference/mesh.h:18-133 (host preprocessing, C++ class bz::Mesh behind the C ABI)"""
+
+    def __init__(self, handle=None):
+        self.lib = load()
+        if handle is None:
+            handle = _vp()
+            _check(self.lib.bz_mesh_create(C.byref(handle)))
+        self.h = handle
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.bz_mesh_destroy(self.h)
+            self.h = None
+
+    def clone(self):
+        out = _vp()
+        _check(self.lib.bz_mesh_clone(self.h, C.byref(out)))
+        return Mesh(out)
+
+    def make_ellipsoid(self, sectors, belts, size):
+        _check(self.lib.bz_mesh_make_ellipsoid(self.h, sectors, belts, C.byref((_f * 3)(*[float(x) for x in size]))))
+        return self
+
+    def make_unit_sphere(self, sectors, belts):
+        _check(self.lib.bz_mesh_make_unit_sphere(self.h, sectors, belts))
+        return self
+
+    def read_stl(self, path):
+        _check(self.lib.bz_mesh_read_stl(self.h, os.fsencode(path)))
+        return self
+
+    def write_stl(self, path):
+        _check(self.lib.bz_mesh_write_stl(self.h, os.fsencode(path)))
+
+    def set_triangles(self, triangles):
+        t = _np(triangles, np.float32, (-1, 9))
+        _check(self.lib.bz_mesh_set_triangles(self.h, t.ctypes.data_as(_vp), t.shape[0]))
+        return self
+
+    def size(self):
+        n = _u32(0)
+        _check(self.lib.bz_mesh_size(self.h, C.byref(n)))
+        return n.value
+
+    def triangles(self):
+        out = np.zeros((self.size(), 3, 3), np.float32)
+        _check(self.lib.bz_mesh_get_triangles(self.h, out.ctypes.data_as(_vp)))
+        return out
+
+    def transform(self, matrix, displacement):
+        m, d = _np(matrix, np.float32, (3, 3)), _np(displacement, np.float32, (3,))
+        _check(self.lib.bz_mesh_transform(self.h, m.ctypes.data_as(_vp), d.ctypes.data_as(_vp)))
+        return self
+
+    def translate(self, x, y, z):
+        return self.transform(np.eye(3, dtype=np.float32), (x, y, z))
+
+    def scale(self, factor):
+        return self.transform(np.eye(3, dtype=np.float32) * np.float32(factor), (0.0, 0.0, 0.0))
+
+    def split_triangles(self, divisor):
+        _check(self.lib.bz_mesh_split_triangles(self.h, int(divisor)))
+        return self
+
+    def split_triangles_by_side(self, max_side):
+        _check(self.lib.bz_mesh_split_triangles_by_side(self.h, float(max_side)))
+        return self
+
+    def standardize_vertices(self):
+        _check(self.lib.bz_mesh_standardize_vertices(self.h))
+        return self
+
+    def standardize_normals(self):
+        _check(self.lib.bz_mesh_standardize_normals(self.h))
+        return self
+
+    def neighbours(self):
+        """getFace2neighbours -> (fellow[n,3] u32, starts[n,3] u8)"""
+        n = _u32(0)
+        _check(self.lib.bz_mesh_neighbour_count(self.h, C.byref(n)))
+        fellow, starts = np.zeros((n.value, 3), np.uint32), np.zeros((n.value, 3), np.uint8)
+        _check(self.lib.bz_mesh_get_face2neighbours(self.h, fellow.ctypes.data_as(_vp), starts.ctypes.data_as(_vp)))
+        return fellow, starts
+
+    def corner_normals(self):
+        """getVertex2averageNormals looked up per corner -> [n,3,3]"""
+        out = np.zeros((self.size(), 3, 3), np.float32)
+        _check(self.lib.bz_mesh_get_corner_normals(self.h, out.ctypes.data_as(_vp)))
+        return out
+
+
+class BezierMesh:
+    """BezierMesh(mesh) -- reference/bezierMesh.h:10-45 (C++ class bz::BezierMesh behind the C ABI)"""
+
+    def __init__(self, mesh):
+        self.lib = load()
+        handle = _vp()
+        _check(self.lib.bz_bezier_create(mesh.h, C.byref(handle)))
+        self.h = handle
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.bz_bezier_destroy(self.h)
+            self.h = None
+
+    def size(self):
+        n = _u32(0)
+        _check(self.lib.bz_bezier_size(self.h, C.byref(n)))
+        return n.value
+
+    def patches(self):
+        """(n, 64) float32 view of the bz_patch table; columns 16:19 hold the uint32 neighbours"""
+        out = np.zeros((self.size(), PATCH_WORDS), np.float32)
+        _check(self.lib.bz_bezier_get_patches(self.h, out.ctypes.data_as(_vp)))
+        return out
+
+    def interpolate(self, divisor):
+        out = _vp()
+        _check(self.lib.bz_bezier_interpolate(self.h, int(divisor), C.byref(out)))
+        return Mesh(out)
+
+    def split_thick(self):
+        out = _vp()
+        _check(self.lib.bz_bezier_split_thick(self.h, C.byref(out)))
+        return Mesh(out)
+
+
 class BezierLens:
     """BezierLens(ri, bezier_mesh) -- reference/bezierLens.h:14-28.
 
@@ -169,16 +322,19 @@ class BezierLens:
 
     def __init__(self, ri, patches, device=0):
         self.lib = load()
-        table = patches.patches() if hasattr(patches, "patches") else patches
-        table = np.ascontiguousarray(table, dtype=np.float32)
-        if table.size == 0:
-            table = table.reshape(0, PATCH_WORDS)
-        assert table.ndim == 2 and table.shape[1] == PATCH_WORDS
         self.device = device
         self.ri = float(ri)
-        self.patch_count = table.shape[0]
         handle = _vp()
-        _check(self.lib.bz_lens_create(table.ctypes.data_as(_vp), table.shape[0], self.ri, device, C.byref(handle)))
+        if isinstance(patches, BezierMesh):
+            self.patch_count = patches.size()
+            _check(self.lib.bz_lens_create_from_bezier(patches.h, self.ri, device, C.byref(handle)))
+        else:
+            table = np.ascontiguousarray(patches, dtype=np.float32)
+            if table.size == 0:
+                table = table.reshape(0, PATCH_WORDS)
+            assert table.ndim == 2 and table.shape[1] == PATCH_WORDS
+            self.patch_count = table.shape[0]
+            _check(self.lib.bz_lens_create(table.ctypes.data_as(_vp), table.shape[0], self.ri, device, C.byref(handle)))
         self.h = handle
 
     def close(self):

@@ -11,6 +11,7 @@
 #include "bz_capi.h"
 #include "bz_device.h"
 #include "../host/bz_bvh.h"
+#include "../host/bz_error.h"
 
 cudaError_t bz_launch_trace(int job, bool brute, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream);
 cudaError_t bz_launch_resolve(const uint32_t *accum, uint8_t *rgba, uint64_t pixels, uint32_t spp, cudaStream_t stream);
@@ -20,7 +21,8 @@ int bz_trace_threads(void);
 
 static thread_local std::string gError;
 
-static int bz_fail(int code, const std::string &text) {
+// shared with host/bz_host_capi.cpp (declared in host/bz_error.h)
+int bz_fail(int code, const std::string &text) {
   gError = text;
   return code;
 }

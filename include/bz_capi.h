@@ -100,6 +100,8 @@ typedef struct bz_stats {
 } bz_stats;
 
 typedef struct bz_lens bz_lens;
+typedef struct bz_mesh bz_mesh;       /* host object: Mesh,       reference/mesh.h:18-133 */
+typedef struct bz_bezier bz_bezier;   /* host object: BezierMesh, reference/bezierMesh.h:10-45 */
 
 /* intersect strategy of a lens handle */
 #define BZ_MODE_BRUTE   0u   /* every ray tests every patch, reference loop order (bezierMesh.cpp:211) */
@@ -112,6 +114,41 @@ uint32_t bz_sizeof_patch(void);
 uint32_t bz_sizeof_camera(void);
 uint32_t bz_sizeof_scene(void);
 uint32_t bz_sizeof_stats(void);
+
+/* ---- host preprocessing (C++ classes bz::Mesh / bz::BezierMesh in cuda-bezier-triangle-raytracer_b200/host) ----
+ * Mesh, reference/mesh.h:50-100.  Triangles are n x 3 corners x 3 floats.  Preprocessing errors
+ * (e.g. the reference's `throw "Vertex on edge detected."`, mesh.cpp:204; std::runtime_error from the
+ * STL reader; std::out_of_range when standardizeNormals was skipped, bezierMesh.cpp:17-18) come back
+ * as BZ_ERR_PREPROCESS with the text in bz_last_error(). */
+int  bz_mesh_create(bz_mesh **out_mesh);
+int  bz_mesh_destroy(bz_mesh *mesh);
+int  bz_mesh_clone(const bz_mesh *mesh, bz_mesh **out_mesh);
+int  bz_mesh_make_ellipsoid(bz_mesh *mesh, int32_t sectors, int32_t belts, const float size[3]);   /* mesh.h:99 */
+int  bz_mesh_make_unit_sphere(bz_mesh *mesh, int32_t sectors, int32_t belts);                        /* mesh.h:100 */
+int  bz_mesh_read_stl(bz_mesh *mesh, const char *path);                                              /* mesh.cpp:399-415 */
+int  bz_mesh_write_stl(const bz_mesh *mesh, const char *path);                                       /* mesh.cpp:419-430 */
+int  bz_mesh_set_triangles(bz_mesh *mesh, const float *triangles, uint32_t count);
+int  bz_mesh_size(const bz_mesh *mesh, uint32_t *out_count);
+int  bz_mesh_get_triangles(const bz_mesh *mesh, float *out_triangles);
+int  bz_mesh_transform(bz_mesh *mesh, const float matrix_row_major[9], const float displacement[3]); /* mesh.cpp:361-367 */
+int  bz_mesh_split_triangles(bz_mesh *mesh, int32_t divisor);                                        /* mesh.cpp:389-395 */
+int  bz_mesh_split_triangles_by_side(bz_mesh *mesh, float max_side);                                 /* mesh.cpp:375-385 */
+int  bz_mesh_standardize_vertices(bz_mesh *mesh);                                                    /* mesh.cpp:72-91 */
+int  bz_mesh_standardize_normals(bz_mesh *mesh);                                                     /* mesh.cpp:310-357 */
+/* getFace2neighbours (mesh.h:68): out_fellow n x 3 u32, out_starts n x 3 u8; the count is 0 before standardizeNormals */
+int  bz_mesh_neighbour_count(const bz_mesh *mesh, uint32_t *out_count);
+int  bz_mesh_get_face2neighbours(const bz_mesh *mesh, uint32_t *out_fellow, uint8_t *out_starts);
+/* getVertex2averageNormals (mesh.h:69) looked up for every corner: n x 3 x 3 floats */
+int  bz_mesh_get_corner_normals(const bz_mesh *mesh, float *out_normals);
+
+/* BezierMesh(Mesh const&), reference/bezierMesh.h:24, bezierMesh.cpp:4-34 */
+int  bz_bezier_create(const bz_mesh *mesh, bz_bezier **out_bezier);
+int  bz_bezier_destroy(bz_bezier *bezier);
+int  bz_bezier_size(const bz_bezier *bezier, uint32_t *out_count);
+int  bz_bezier_get_patches(const bz_bezier *bezier, bz_patch *out_patches);
+int  bz_bezier_interpolate(const bz_bezier *bezier, int32_t divisor, bz_mesh **out_mesh);           /* bezierMesh.cpp:55-66 */
+int  bz_bezier_split_thick(const bz_bezier *bezier, bz_mesh **out_mesh);                            /* bezierMesh.cpp:79-198 */
+int  bz_lens_create_from_bezier(const bz_bezier *bezier, float refractive_index, int device, bz_lens **out_lens);
 
 /* BezierLens(float aRi, BezierMesh const&)  -- reference/bezierLens.h:23-24.
  * Uploads the patch records to `device`, repacks them into SoA float4 streams and builds the
