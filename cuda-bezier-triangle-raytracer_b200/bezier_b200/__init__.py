@@ -102,6 +102,7 @@ SIGNATURES = {
     "bz_render_host": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _vp, C.POINTER(Stats)]),
     "bz_striped_rows": (_u32, [_u32, _u32, _u32, _u32]),
     "bz_render_striped": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _u32, _vp, _vp, _vp]),
+    "bz_assemble_stripes": (_int, [_vp, _u32, _u32, _u32, _u32, _u32, _vp, _vp]),
     "bz_fp32_peak_probe": (_int, [_int, C.POINTER(_f), C.POINTER(_f)]),
     "bz_mesh_create": (_int, [C.POINTER(_vp)]),
     "bz_mesh_destroy": (_int, [_vp]),
@@ -394,6 +395,12 @@ class BezierLens:
         _check(self.lib.bz_render_host(self.h, C.byref(camera), C.byref(scene), row0, row1, rgba.ctypes.data_as(_vp), C.byref(stats)))
         return rgba, stats
 
+    def render_host_into(self, camera, scene, host_ptr, row0=0, row1=None, stats=None):
+        """bz_render_host into caller-owned host memory (e.g. a pinned buffer); `stats` is a Stats to accumulate into"""
+        row1 = camera.height if row1 is None else row1
+        _check(self.lib.bz_render_host(self.h, C.byref(camera), C.byref(scene), row0, row1, C.c_void_p(int(host_ptr)),
+                                       None if stats is None else C.byref(stats)))
+
     # ---- device-buffer entry points (torch CUDA tensors, asynchronous on the stream) ----
 
     def refract_device(self, start, direction, expected, out_start, out_dir, out_status, out_patch=None, stream=None):
@@ -408,6 +415,11 @@ class BezierLens:
     def render_striped_device(self, camera, scene, stripe_rows, rank, ranks, rgba, stats=None, stream=None):
         _check(self.lib.bz_render_striped(self.h, C.byref(camera), C.byref(scene), stripe_rows, rank, ranks, _ptr(rgba), _ptr(stats),
                                           _stream_handle(stream)))
+
+
+def assemble_stripes_device(bands, band_rows, width, height, stripe_rows, ranks, rgba, stream=None):
+    """gathered stripe buffers [ranks, band_rows, width, 4] -> image [height, width, 4] (device tensors)"""
+    _check(load().bz_assemble_stripes(_ptr(bands), band_rows, width, height, stripe_rows, ranks, _ptr(rgba), _stream_handle(stream)))
 
 
 def generate_rays_device(camera, start, direction, row0=0, row1=None, stream=None):

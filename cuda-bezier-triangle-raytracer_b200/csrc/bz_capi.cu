@@ -16,6 +16,8 @@
 cudaError_t bz_launch_trace(int job, bool brute, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream);
 cudaError_t bz_launch_resolve(const uint32_t *accum, uint8_t *rgba, uint64_t pixels, uint32_t spp, cudaStream_t stream);
 cudaError_t bz_launch_raygen(const bz_camera &cam, uint32_t row0, uint64_t count, float *start, float *dir, cudaStream_t stream);
+cudaError_t bz_launch_assemble(const uint8_t *bands, uint32_t band_rows, uint32_t width, uint32_t height, uint32_t stripe_rows,
+                               uint32_t ranks, uint8_t *image, cudaStream_t stream);
 cudaError_t bz_launch_fma_probe(float *sink, uint32_t iters, int grid, cudaStream_t stream);
 int bz_trace_threads(void);
 
@@ -117,10 +119,11 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
     std::memcpy(w + 33, p.divider, 12u * sizeof(float));
     std::memcpy(w + 45, p.neighbours, 3u * sizeof(uint32_t));
   }
-  size_t const slots = bvh.order.size() + bvh.always.size();
-  std::vector<float> leaf(slots * 16u);
-  for(size_t k = 0u; k < bvh.order.size(); ++k) { bz_pack_cull(h_patches[bvh.order[k]], bvh.order[k], leaf.data() + k * 16u); }
-  for(size_t k = 0u; k < bvh.always.size(); ++k) { bz_pack_cull(h_patches[bvh.always[k]], bvh.always[k], leaf.data() + (bvh.order.size() + k) * 16u); }
+  std::vector<uint32_t> slot2patch(bvh.order);
+  slot2patch.insert(slot2patch.end(), bvh.wide.begin(), bvh.wide.end());
+  slot2patch.insert(slot2patch.end(), bvh.always.begin(), bvh.always.end());
+  std::vector<float> leaf(slot2patch.size() * 16u);
+  for(size_t k = 0u; k < slot2patch.size(); ++k) { bz_pack_cull(h_patches[slot2patch[k]], slot2patch[k], leaf.data() + k * 16u); }
 
   bz_lens *lens = new bz_lens();
   std::memset(lens, 0, sizeof(*lens));
@@ -156,7 +159,9 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   lens->tables.nodes = lens->d_nodes;
   lens->tables.patch_count = patch_count;
   lens->tables.node_count = (uint32_t)(bvh.nodes.size() / 32u);
-  lens->tables.always_first = (uint32_t)bvh.order.size();
+  lens->tables.wide_first = (uint32_t)bvh.order.size();
+  lens->tables.always_first = (uint32_t)(bvh.order.size() + bvh.wide.size());
+  lens->tables.origin_limit = bvh.origin_limit;
   lens->tables.always_count = (uint32_t)bvh.always.size();
   lens->tables.ri = refractive_index;
   lens->tables.extent = bvh.extent;
@@ -357,6 +362,17 @@ int bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *sc
   if(stripe_rows == 0u || ranks == 0u || rank >= ranks) { return bz_fail(BZ_ERR_INVALID, "bad stripe layout"); }
   uint32_t const rows = bz_striped_rows(camera->height, stripe_rows, rank, ranks);
   return bz_render_common(lens, camera, scene, 0u, rows, stripe_rows, rank, ranks, d_rgba, d_stats, (cudaStream_t)stream);
+}
+
+int bz_assemble_stripes(const uint8_t *d_bands, uint32_t band_rows, uint32_t width, uint32_t height, uint32_t stripe_rows,
+                        uint32_t ranks, uint8_t *d_rgba, void *stream) {
+  if(stripe_rows == 0u || ranks == 0u) { return bz_fail(BZ_ERR_INVALID, "bad stripe layout"); }
+  if((uint64_t)width * height != 0u && (d_bands == nullptr || d_rgba == nullptr)) { return bz_fail(BZ_ERR_INVALID, "null image buffer"); }
+  for(uint32_t rank = 0u; rank < ranks; ++rank) {
+    if(bz_striped_rows(height, stripe_rows, rank, ranks) > band_rows) { return bz_fail(BZ_ERR_INVALID, "band_rows too small for the stripe layout"); }
+  }
+  BZ_CUDA(bz_launch_assemble(d_bands, band_rows, width, height, stripe_rows, ranks, d_rgba, (cudaStream_t)stream));
+  return BZ_OK;
 }
 
 int bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,

@@ -5,8 +5,9 @@
 //            [0] plane n.xyz, k   [1] Binv row0.xyz, hIn   [2] Binv row1.xyz, hOut   [3] Binv row2.xyz, patch index bits
 //   newton  12 float4 per patch, ORIGINAL patch order   stage-B record  (bezierTriangle.h:65,68,73,80)
 //            words 0..29 control points, 30..32 dirB, 33..44 divider planes (n.xyz,k) x3, 45..47 neighbours
-//   leaf     4 float4 per leaf slot: the cull records again, in BVH leaf order, followed by the
-//            "always" segment (patches the cull cannot bound, tested for every ray)
+//   leaf     4 float4 per leaf slot: the cull records again, in BVH leaf order, followed by the "wide"
+//            segment (tested directly only by rays starting beyond origin_limit) and the "always"
+//            segment (patches the cull cannot bound, tested for every ray)
 //   nodes    8 float4 per 4-wide BVH node: lo.x[4] hi.x[4] lo.y[4] hi.y[4] lo.z[4] hi.z[4] child[4] pad
 //            child > 0: inner node index; child < 0: leaf, ~child = first_slot << 3 | count; 0: empty
 #ifndef BZ_DEVICE_H
@@ -28,8 +29,11 @@ struct bz_tables {
   const float4 *nodes;
   uint32_t patch_count;
   uint32_t node_count;
+  uint32_t wide_first;     // slots [wide_first, always_first): copies of the ill-conditioned patches whose grown boxes are
+                           // only valid for ray origins with |s|_1 <= origin_limit; farther rays test them directly
   uint32_t always_first;   // slot range [always_first, always_first + always_count) of `leaf`
   uint32_t always_count;
+  float    origin_limit;
   float    ri;
   float    extent;         // max |coordinate| over the flat triangles: sizes the per-ray cull slack
 };

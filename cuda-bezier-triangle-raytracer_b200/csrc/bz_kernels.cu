@@ -321,15 +321,19 @@ __global__ void __launch_bounds__(BZ_NT, 2) bz_trace_kernel(const bz_tables T, c
         }
         if(node < 0 && sp > 0) { node = stack[--sp]; }
       }
-      for(uint32_t j = 0u; j < T.always_count; ++j) {
+      // patches the hierarchy does not vouch for: the always segment, plus the wide segment for far origins
+      const bool far_origin = !(fabsf(s.x) + fabsf(s.y) + fabsf(s.z) <= T.origin_limit);
+      const uint32_t direct_first = far_origin ? T.wide_first : T.always_first;
+      const uint32_t direct_end = T.always_first + T.always_count;
+      for(uint32_t j = direct_first; j < direct_end; ++j) {
         bz_cull_rec c;
-        uint32_t patch = bz_load_cull(T.leaf, T.always_first + j, c);
+        uint32_t patch = bz_load_cull(T.leaf, j, c);
         float cosine, distance;
         if(bz_stage_a(c, s, d, true, cosine, distance)) {
           bz_push_candidate(sm, T, t, patch, s, d, ikey, ihit, ipatch, c_a, c_b);
         }
       }
-      c_a += T.always_count;
+      c_a += direct_end - direct_first;
     }
     __syncthreads();
 
@@ -489,6 +493,21 @@ __global__ void bz_resolve_kernel(const uint32_t *accum, uchar4 *rgba, uint64_t 
   }
 }
 
+// Multi-GPU image assembly: `bands` holds, per rank, that rank's stripes in image order (band_rows rows reserved per
+// rank, as an all-gather of equally sized buffers leaves them); every image row is copied to its place.  One uint
+// (one RGBA pixel) per thread, rows are contiguous so the copies coalesce.
+__global__ void bz_assemble_kernel(const uint32_t *bands, uint32_t band_rows, uint32_t width, uint32_t height, uint32_t stripe_rows,
+                                   uint32_t ranks, uint32_t *image) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if(i < (uint64_t)width * height) {
+    uint32_t row = (uint32_t)(i / width), px = (uint32_t)(i - (uint64_t)row * width);
+    uint32_t stripe = row / stripe_rows;
+    uint32_t rank = stripe % ranks;
+    uint32_t local = (stripe / ranks) * stripe_rows + row % stripe_rows;
+    image[i] = bands[((uint64_t)rank * band_rows + local) * width + px];
+  }
+}
+
 // K1 alone: primary rays of a row band into n x 3 float arrays (bz_generate_rays).
 __global__ void bz_raygen_kernel(const bz_camera cam, uint32_t row0, uint64_t count, float *start, float *dir) {
   uint64_t id = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -536,6 +555,14 @@ cudaError_t bz_launch_resolve(const uint32_t *accum, uint8_t *rgba, uint64_t pix
 cudaError_t bz_launch_raygen(const bz_camera &cam, uint32_t row0, uint64_t count, float *start, float *dir, cudaStream_t stream) {
   if(count == 0u) { return cudaSuccess; }
   bz_raygen_kernel<<<(unsigned)((count + 255u) / 256u), 256, 0, stream>>>(cam, row0, count, start, dir);
+  return cudaGetLastError();
+}
+
+cudaError_t bz_launch_assemble(const uint8_t *bands, uint32_t band_rows, uint32_t width, uint32_t height, uint32_t stripe_rows,
+                               uint32_t ranks, uint8_t *image, cudaStream_t stream) {
+  uint64_t const pixels = (uint64_t)width * height;
+  if(pixels == 0u) { return cudaSuccess; }
+  bz_assemble_kernel<<<(unsigned)((pixels + 255u) / 256u), 256, 0, stream>>>((const uint32_t*)bands, band_rows, width, height, stripe_rows, ranks, (uint32_t*)image);
   return cudaGetLastError();
 }
 

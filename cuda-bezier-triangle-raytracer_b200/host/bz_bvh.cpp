@@ -7,9 +7,13 @@
 // the box test is conservative with respect to the FP32 rounding of stage A.  That slack is applied
 // per ray in the kernel (it depends on the ray's origin); here the only per-patch input is the
 // conditioning kappa = max_i |row_i(Binv)|_1 * altitude_i, which scales the barycentric rounding
-// error into a distance.  Patches with kappa > 16 (underlying plane passing close to the origin, or
-// a degenerate inverse) are not put into the hierarchy at all: they go to the "always" segment and
-// are tested for every ray, as the reference does.
+// error into a distance: the in-plane error of the inside test is at most kappa * 2^-19 * (|s|_1 + 2 extent)
+// for a ray starting at s.  The kernel's per-ray slack covers kappa <= 16.  Patches with
+// 16 < kappa <= 65536 ("wide": underlying plane seen at a grazing angle from the origin) stay in the
+// hierarchy with their boxes grown on the host by the remaining (kappa - 16) share, evaluated for the
+// largest ray origin the hierarchy vouches for (origin_limit); a ray starting farther out tests them
+// directly.  Patches with a larger or non-finite kappa go to the "always" segment and are tested for
+// every ray, as the reference does.
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -40,6 +44,9 @@ struct Binary {
 
 constexpr int cBins = 16;
 constexpr double cKappaLimit = 16.0;
+constexpr double cKappaWideLimit = 65536.0;
+constexpr double cSlackUnit = 1.9073486328125e-06;     // 2^-19; the kernel's per-ray slack is cKappaLimit * cSlackUnit * (|s|_1 + 2 extent)
+constexpr double cOriginLimitFactor = 64.0;
 
 struct Builder {
   std::vector<Box> boxes;            // per primitive (index into prims)
@@ -141,8 +148,11 @@ void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out) {
   out.always.clear();
   out.extent = 0.0f;
   out.depth = 0u;
+  out.wide.clear();
+  out.origin_limit = 0.0f;
   Builder b;
   std::vector<uint32_t> prims;     // primitive -> patch
+  std::vector<double> kappas(count, std::numeric_limits<double>::infinity());
   for(uint32_t i = 0u; i < count; ++i) {
     const bz_patch &p = patches[i];
     const float *v[3] = { p.control[0], p.control[1], p.control[2] };
@@ -150,37 +160,47 @@ void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out) {
     for(int a = 0; a < 3; ++a) {
       for(int k = 0; k < 3; ++k) { finite = finite && std::isfinite(v[a][k]); }
     }
-    double kappa = std::numeric_limits<double>::infinity();
-    if(finite) {
-      double e[3][3];   // e[i] = edge opposite vertex i
-      for(int k = 0; k < 3; ++k) {
-        e[0][k] = double(v[2][k]) - v[1][k];
-        e[1][k] = double(v[0][k]) - v[2][k];
-        e[2][k] = double(v[1][k]) - v[0][k];
-      }
-      double cx = e[2][1] * -e[1][2] - e[2][2] * -e[1][1];
-      double cy = e[2][2] * -e[1][0] - e[2][0] * -e[1][2];
-      double cz = e[2][0] * -e[1][1] - e[2][1] * -e[1][0];
-      double const twiceArea = std::sqrt(cx * cx + cy * cy + cz * cz);
-      kappa = 0.0;
-      for(int i3 = 0; i3 < 3; ++i3) {
-        double const edge = std::sqrt(e[i3][0] * e[i3][0] + e[i3][1] * e[i3][1] + e[i3][2] * e[i3][2]);
-        double const altitude = twiceArea / edge;
-        double const row = std::fabs(double(p.bary_inv[i3][0])) + std::fabs(double(p.bary_inv[i3][1])) + std::fabs(double(p.bary_inv[i3][2]));
-        kappa = std::max(kappa, row * altitude);
-        if(!(row * altitude == row * altitude)) { kappa = std::numeric_limits<double>::infinity(); }
-      }
-      for(int a = 0; a < 3; ++a) {
-        for(int k = 0; k < 3; ++k) { out.extent = std::max(out.extent, std::fabs(v[a][k])); }
-      }
+    if(!finite) { continue; }
+    double e[3][3];   // e[i] = edge opposite vertex i
+    for(int k = 0; k < 3; ++k) {
+      e[0][k] = double(v[2][k]) - v[1][k];
+      e[1][k] = double(v[0][k]) - v[2][k];
+      e[2][k] = double(v[1][k]) - v[0][k];
     }
-    if(!(kappa <= cKappaLimit)) {
+    double cx = e[2][1] * -e[1][2] - e[2][2] * -e[1][1];
+    double cy = e[2][2] * -e[1][0] - e[2][0] * -e[1][2];
+    double cz = e[2][0] * -e[1][1] - e[2][1] * -e[1][0];
+    double const twiceArea = std::sqrt(cx * cx + cy * cy + cz * cz);
+    double kappa = 0.0;
+    for(int i3 = 0; i3 < 3; ++i3) {
+      double const edge = std::sqrt(e[i3][0] * e[i3][0] + e[i3][1] * e[i3][1] + e[i3][2] * e[i3][2]);
+      double const altitude = twiceArea / edge;
+      double const row = std::fabs(double(p.bary_inv[i3][0])) + std::fabs(double(p.bary_inv[i3][1])) + std::fabs(double(p.bary_inv[i3][2]));
+      kappa = std::max(kappa, row * altitude);
+      if(!(row * altitude == row * altitude)) { kappa = std::numeric_limits<double>::infinity(); }
+    }
+    kappas[i] = kappa;
+    for(int a = 0; a < 3; ++a) {
+      for(int k = 0; k < 3; ++k) { out.extent = std::max(out.extent, std::fabs(v[a][k])); }
+    }
+  }
+  out.origin_limit = static_cast<float>(cOriginLimitFactor * out.extent);
+  for(uint32_t i = 0u; i < count; ++i) {
+    const bz_patch &p = patches[i];
+    const float *v[3] = { p.control[0], p.control[1], p.control[2] };
+    if(!(kappas[i] <= cKappaWideLimit)) {
       out.always.push_back(i);
       continue;
     }
     Box box;
     box.reset();
     for(int a = 0; a < 3; ++a) { box.grow(v[a]); }
+    if(kappas[i] > cKappaLimit) {
+      // 1.5: the sum below is rounded to float twice (grow, then the kernel's own arithmetic)
+      float const grow = static_cast<float>(1.5 * (kappas[i] - cKappaLimit) * cSlackUnit * (double(out.origin_limit) + 2.0 * out.extent));
+      for(int k = 0; k < 3; ++k) { box.lo[k] -= grow; box.hi[k] += grow; }
+      out.wide.push_back(i);
+    }
     b.boxes.push_back(box);
     for(int k = 0; k < 3; ++k) { b.centroid.push_back((v[0][k] + v[1][k] + v[2][k]) / 3.0f); }
     prims.push_back(i);

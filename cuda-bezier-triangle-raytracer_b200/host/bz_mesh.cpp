@@ -474,8 +474,36 @@ void Mesh::readMesh(std::string const &aFilename) {
       raw.push_back(Triangle{Vec3{values[3], values[4], values[5]}, Vec3{values[6], values[7], values[8]}, Vec3{values[9], values[10], values[11]}});
     }
   }
+  // The reader merges corners that compare equal (so -0 and +0 are one coordinate) onto the first of each run of
+  // a std::sort by (x, y, z), and drops triangles that end up with two identical corners (stl_reader.h:449-506).
+  // The same sort on the same sequence picks the same representative, signed zeros included.
+  struct Corner {
+    float data[3];
+    int32_t index;
+    bool operator<(Corner const &aC) const {
+      return data[0] < aC.data[0] || (data[0] == aC.data[0] && data[1] < aC.data[1]) || (data[0] == aC.data[0] && data[1] == aC.data[1] && data[2] < aC.data[2]);
+    }
+    bool same(Corner const &aC) const { return data[0] == aC.data[0] && data[1] == aC.data[1] && data[2] == aC.data[2]; }
+  };
+  std::vector<Corner> corners;
+  corners.reserve(raw.size() * 3u);
   for(auto const &triangle : raw) {
-    if(triangle[0] != triangle[1] && triangle[0] != triangle[2] && triangle[1] != triangle[2]) { mMesh.push_back(triangle); }
+    for(auto const &vertex : triangle) { corners.push_back(Corner{{vertex.x, vertex.y, vertex.z}, static_cast<int32_t>(corners.size())}); }
+  }
+  if(corners.empty()) { return; }
+  std::sort(corners.begin(), corners.end());
+  std::vector<uint32_t> merged(corners.size());       // corner in file order -> position of its representative
+  size_t runStart = 0u;
+  for(size_t i = 0u; i < corners.size(); ++i) {
+    if(i > 0u && !corners[i].same(corners[i - 1u])) { runStart = i; }
+    merged[static_cast<size_t>(corners[i].index)] = static_cast<uint32_t>(runStart);
+  }
+  for(size_t t = 0u; t < raw.size(); ++t) {
+    uint32_t const a = merged[3u * t], b = merged[3u * t + 1u], c = merged[3u * t + 2u];
+    if(a != b && a != c && b != c) {
+      auto at = [&corners](uint32_t aI) { return Vec3{corners[aI].data[0], corners[aI].data[1], corners[aI].data[2]}; };
+      mMesh.push_back(Triangle{at(a), at(b), at(c)});
+    }
   }
 }
 

@@ -195,6 +195,11 @@ uint32_t bz_striped_rows(uint32_t height, uint32_t stripe_rows, uint32_t rank, u
 int  bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t stripe_rows, uint32_t rank,
                        uint32_t ranks, uint8_t *d_rgba, bz_stats *d_stats, void *stream);
 
+/* After an all-gather of the ranks' stripe buffers (each padded to band_rows rows; NCCL over NVLink in bench.py):
+ * d_bands = ranks x band_rows x width x 4 bytes -> d_rgba = height x width x 4 bytes in image order. */
+int  bz_assemble_stripes(const uint8_t *d_bands, uint32_t band_rows, uint32_t width, uint32_t height, uint32_t stripe_rows,
+                         uint32_t ranks, uint8_t *d_rgba, void *stream);
+
 /* Cull-hierarchy facts of a lens: out[0] = 4-wide nodes, out[1] = levels, out[2] = patches in the
  * always-tested segment, out[3] = SM count of the device. */
 int  bz_lens_info(const bz_lens *lens, uint32_t out[4]);

@@ -108,6 +108,10 @@ void shim_intersect_batch(const bz_patch *patches, uint32_t count, const float *
           visited[0] += (code & 7u);
         }
       }
+      if(!(std::fabs(s.x) + std::fabs(s.y) + std::fabs(s.z) <= bvh.origin_limit)) {
+        for(uint32_t i : bvh.wide) { candidate(patches, i, s, d, best); }
+        visited[0] += bvh.wide.size();
+      }
       for(uint32_t i : bvh.always) { candidate(patches, i, s, d, best); }
       visited[0] += bvh.always.size();
     }
@@ -142,6 +146,16 @@ void shim_bvh_info(const bz_patch *patches, uint32_t count, uint32_t *out) {
   out[1] = bvh.depth;
   out[2] = (uint32_t)bvh.always.size();
   out[3] = (uint32_t)bvh.order.size();
+  out[4] = (uint32_t)bvh.wide.size();
+}
+
+// indices of the wide patches (hierarchy members with grown boxes); returns their count
+uint32_t shim_bvh_wide(const bz_patch *patches, uint32_t count, uint32_t *out, uint32_t capacity, float *out_origin_limit) {
+  bz_bvh bvh;
+  bz_build_bvh(patches, count, bvh);
+  for(uint32_t i = 0u; i < bvh.wide.size() && i < capacity; ++i) { out[i] = bvh.wide[i]; }
+  *out_origin_limit = bvh.origin_limit;
+  return (uint32_t)bvh.wide.size();
 }
 
 }

@@ -36,3 +36,36 @@ def test_far_origin_rays_stay_exact(oracle_built, shim):
     ref = bzoracle.intersect(patches, o, d, threads=8)
     culled, _ = common.shim_intersect(shim, patches, o, d, 1)
     common.assert_same_hits(ref, culled, "far")
+
+
+def test_wide_patches_stay_exact(oracle_built, shim):
+    """ill-conditioned patches (kappa > 16) sit in the hierarchy with grown boxes: rays aimed at them, from
+    origins inside and outside the origin limit, must still see exactly the reference's candidates"""
+    import ctypes as C
+    import bzoracle
+    mesh, bezier, patches = common.ref_config("ellipsoid181x91")
+    wide = np.zeros(4096, np.uint32)
+    limit = C.c_float(0.0)
+    shim.shim_bvh_wide.restype = C.c_uint32
+    count = shim.shim_bvh_wide(patches.ctypes.data_as(C.c_void_p), C.c_uint32(patches.shape[0]), wide.ctypes.data_as(C.c_void_p),
+                               C.c_uint32(wide.size), C.byref(limit))
+    assert 0 < count <= wide.size and limit.value > 0
+    wide = wide[:count]
+    rng = np.random.default_rng(21)
+    n = 4000
+    pick = wide[rng.integers(0, count, n)]
+    cp = patches[pick][:, 20:50].reshape(n, 10, 3)
+    w = rng.dirichlet((1.0, 1.0, 1.0), n).astype(np.float32) * 1.4 - 0.133     # a little beyond the flat triangle too
+    target = (cp[:, 0] * w[:, :1] + cp[:, 1] * w[:, 1:2] + cp[:, 2] * w[:, 2:3]).astype(np.float64)
+    o = rng.normal(size=(n, 3))
+    o /= np.linalg.norm(o, axis=1, keepdims=True)
+    radius = np.where(np.arange(n) % 2 == 0, 12.0, limit.value * 1.5)          # inside / outside the origin limit
+    o = target + o * radius[:, None]
+    d = target - o
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    o = o.astype(np.float32)
+    ref = bzoracle.intersect(patches, o, d, threads=8)
+    culled, _ = common.shim_intersect(shim, patches, o, d, 1)
+    assert int((ref["what"] == 4).sum()) > 500
+    assert int(np.isin(ref["patch"], wide).sum()) > 50
+    common.assert_same_hits(ref, culled, "wide")
