@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libbz_b200.so")
+LIB_PATH = os.environ.get("BZ_B200_LIB") or os.path.join(os.path.dirname(_HERE), "libbz_b200.so")   # override: debugging builds only
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_PREPROCESS = 0, -1, -2, -3, -4
 STATUS_NONE, STATUS_INSIDE, STATUS_OUTSIDE = 0, 1, 2

@@ -20,6 +20,8 @@ cudaError_t bz_launch_assemble(const uint8_t *bands, uint32_t band_rows, uint32_
                                uint32_t ranks, uint8_t *image, cudaStream_t stream);
 cudaError_t bz_launch_fma_probe(float *sink, uint32_t iters, int grid, cudaStream_t stream);
 int bz_trace_threads(void);
+cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream);
+cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta);
 
 static thread_local std::string gError;
 
@@ -108,7 +110,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
 
   bz_bvh bvh;
   bz_build_bvh(h_patches, patch_count, bvh);
-  if(bvh.depth * 3u + 4u > 64u) { return bz_fail(BZ_ERR_INVALID, "cull hierarchy too deep for the traversal stack"); }
+  static_assert(BZ_LEAF_MAX <= 7, "leaf codes keep the count in 3 bits");
   std::vector<float> cull((size_t)patch_count * 16u), newton((size_t)patch_count * 48u);
   for(uint32_t i = 0u; i < patch_count; ++i) {
     const bz_patch &p = h_patches[i];
@@ -134,9 +136,13 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   cudaError_t e = cudaGetDeviceProperties(&prop, device);
   if(e != cudaSuccess) { delete lens; return bz_fail(BZ_ERR_CUDA, cudaGetErrorString(e)); }
   lens->sm_count = prop.multiProcessorCount;
+  // every table gets 256 zeroed bytes of tail padding: a record fetched one past the end (a load the compiler moved
+  // above its loop test) stays inside the allocation and decodes as a patch no ray can meet (zero normal)
   auto upload = [&](const std::vector<float> &src, float4 **dst) -> cudaError_t {
-    size_t bytes = std::max<size_t>(src.size() * sizeof(float), 16u);
+    size_t bytes = src.size() * sizeof(float) + 256u;
     cudaError_t r = cudaMalloc((void**)dst, bytes);
+    if(r != cudaSuccess) { return r; }
+    r = cudaMemset(*dst, 0, bytes);
     if(r != cudaSuccess) { return r; }
     if(!src.empty()) { r = cudaMemcpy(*dst, src.data(), src.size() * sizeof(float), cudaMemcpyHostToDevice); }
     return r;
@@ -158,7 +164,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   lens->tables.leaf = lens->d_leaf;
   lens->tables.nodes = lens->d_nodes;
   lens->tables.patch_count = patch_count;
-  lens->tables.node_count = (uint32_t)(bvh.nodes.size() / 32u);
+  lens->tables.node_count = (uint32_t)(bvh.nodes.size() / 8u);
   lens->tables.wide_first = (uint32_t)bvh.order.size();
   lens->tables.always_first = (uint32_t)(bvh.order.size() + bvh.wide.size());
   lens->tables.origin_limit = bvh.origin_limit;
@@ -200,11 +206,23 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
   if(desc.ray_count == 0u) { return BZ_OK; }
   BZ_CUDA(cudaMemsetAsync(lens->d_counter, 0, sizeof(unsigned long long), stream));
   desc.next_ray = lens->d_counter;
-  uint64_t const threads = (uint64_t)bz_trace_threads();
-  uint64_t const wanted = (desc.ray_count + threads - 1u) / threads;
-  int const grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * 2u, wanted);
+  bool const brute = (lens->mode == BZ_MODE_BRUTE);
+  int grid;
+  if(brute) {
+    uint64_t const threads = (uint64_t)bz_trace_threads();
+    uint64_t const wanted = (desc.ray_count + threads - 1u) / threads;
+    grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * 2u, wanted);
+  }
+  else {
+    // persistent grid: every resident CTA slot of the device, or fewer when the batch is small
+    int perSm = 0, raysPerCta = 0;
+    BZ_CUDA(bz_warp_trace_occupancy(&perSm, &raysPerCta));
+    uint64_t const wanted = (desc.ray_count + (uint64_t)raysPerCta - 1u) / (uint64_t)raysPerCta;
+    grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * (uint64_t)std::max(perSm, 1), wanted);
+  }
   BZ_CUDA(cudaEventRecord(lens->ev_begin, stream));
-  BZ_CUDA(bz_launch_trace(job, lens->mode == BZ_MODE_BRUTE, lens->tables, desc, grid, stream));
+  if(brute) { BZ_CUDA(bz_launch_trace(job, true, lens->tables, desc, grid, stream)); }
+  else { BZ_CUDA(bz_launch_warp_trace(job, lens->tables, desc, grid, stream)); }
   BZ_CUDA(cudaEventRecord(lens->ev_end, stream));
   lens->last_stream = stream;
   lens->timed = true;

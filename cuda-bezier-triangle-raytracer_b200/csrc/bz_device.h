@@ -8,8 +8,9 @@
 //   leaf     4 float4 per leaf slot: the cull records again, in BVH leaf order, followed by the "wide"
 //            segment (tested directly only by rays starting beyond origin_limit) and the "always"
 //            segment (patches the cull cannot bound, tested for every ray)
-//   nodes    8 float4 per 4-wide BVH node: lo.x[4] hi.x[4] lo.y[4] hi.y[4] lo.z[4] hi.z[4] child[4] pad
-//            child > 0: inner node index; child < 0: leaf, ~child = first_slot << 3 | count; 0: empty
+//   nodes    2 float4 per node of the binary cull hierarchy, depth-first order:
+//            [0] box lo.xyz, skip link (index of the first node after this subtree, taken when the box is missed)
+//            [1] box hi.xyz, leaf code (0: inner node, its first child is the next node; else first_slot << 3 | count)
 #ifndef BZ_DEVICE_H
 #define BZ_DEVICE_H
 
@@ -19,8 +20,8 @@
 
 #define BZ_CULL_F4    4
 #define BZ_NEWTON_F4  12
-#define BZ_NODE_F4    8
-#define BZ_LEAF_MAX   4
+#define BZ_NODE_F4    2
+#define BZ_LEAF_MAX   2     // patches per leaf of the cull hierarchy (host/bz_bvh.cpp builds to this)
 
 struct bz_tables {
   const float4 *cull;

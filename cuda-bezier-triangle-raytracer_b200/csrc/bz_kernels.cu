@@ -27,7 +27,6 @@
 #define BZ_QA        1024
 #define BZ_QB        256
 #define BZ_PAY       11
-#define BZ_STACK     64
 #define BZ_TILE      256
 #define BZ_KEY_NONE  0xffffffffffffffffull
 #define BZ_NSTAT     9
@@ -270,71 +269,6 @@ __global__ void __launch_bounds__(BZ_NT, 2) bz_trace_kernel(const bz_tables T, c
         }
       }
     }
-    else if(live) {
-      // per-ray slack of the box tests: covers the rounding of stage A's in-plane point and barycentrics
-      // for patches whose conditioning is <= 16 (the others sit in the always segment), DESIGN.md
-      float slack = 3.0517578125e-05f * (fabsf(s.x) + fabsf(s.y) + fabsf(s.z) + 2.0f * T.extent);
-      float ix = (fabsf(d.x) > 1e-20f) ? 1.0f / d.x : copysignf(1e20f, d.x);
-      float iy = (fabsf(d.y) > 1e-20f) ? 1.0f / d.y : copysignf(1e20f, d.y);
-      float iz = (fabsf(d.z) > 1e-20f) ? 1.0f / d.z : copysignf(1e20f, d.z);
-      float ax_lo = -(s.x + slack) * ix, ax_hi = -(s.x - slack) * ix;
-      float ay_lo = -(s.y + slack) * iy, ay_hi = -(s.y - slack) * iy;
-      float az_lo = -(s.z + slack) * iz, az_hi = -(s.z - slack) * iz;
-      int stack[BZ_STACK];
-      int sp = 0;
-      int node = (T.node_count != 0u) ? 0 : -1;
-      while(node >= 0) {
-        ++c_nodes;
-        const float4 *p = T.nodes + (size_t)node * BZ_NODE_F4;
-        float4 lox = __ldg(p), hix = __ldg(p + 1), loy = __ldg(p + 2), hiy = __ldg(p + 3), loz = __ldg(p + 4), hiz = __ldg(p + 5);
-        float4 chf = __ldg(p + 6);
-        int child[4] = { __float_as_int(chf.x), __float_as_int(chf.y), __float_as_int(chf.z), __float_as_int(chf.w) };
-        float blox[4] = { lox.x, lox.y, lox.z, lox.w }, bhix[4] = { hix.x, hix.y, hix.z, hix.w };
-        float bloy[4] = { loy.x, loy.y, loy.z, loy.w }, bhiy[4] = { hiy.x, hiy.y, hiy.z, hiy.w };
-        float bloz[4] = { loz.x, loz.y, loz.z, loz.w }, bhiz[4] = { hiz.x, hiz.y, hiz.z, hiz.w };
-        node = -1;
-#pragma unroll
-        for(int k = 0; k < 4; ++k) {
-          if(child[k] == 0) { continue; }
-          float x0 = __fmaf_rn(blox[k], ix, ax_lo), x1 = __fmaf_rn(bhix[k], ix, ax_hi);
-          float y0 = __fmaf_rn(bloy[k], iy, ay_lo), y1 = __fmaf_rn(bhiy[k], iy, ay_hi);
-          float z0 = __fmaf_rn(bloz[k], iz, az_lo), z1 = __fmaf_rn(bhiz[k], iz, az_hi);
-          float tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
-          float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
-          if(!(tnear <= tfar * 1.000001f)) { continue; }
-          if(child[k] > 0) {
-            if(node < 0) { node = child[k]; } else { stack[sp++] = child[k]; }
-          }
-          else {
-            uint32_t code = (uint32_t)(~child[k]);
-            uint32_t first = code >> 3, count = code & 7u;
-            for(uint32_t j = 0u; j < count; ++j) {
-              bz_cull_rec c;
-              uint32_t patch = bz_load_cull(T.leaf, first + j, c);
-              float cosine, distance;
-              if(bz_stage_a(c, s, d, true, cosine, distance)) {
-                bz_push_candidate(sm, T, t, patch, s, d, ikey, ihit, ipatch, c_a, c_b);
-              }
-            }
-            c_a += count;
-          }
-        }
-        if(node < 0 && sp > 0) { node = stack[--sp]; }
-      }
-      // patches the hierarchy does not vouch for: the always segment, plus the wide segment for far origins
-      const bool far_origin = !(fabsf(s.x) + fabsf(s.y) + fabsf(s.z) <= T.origin_limit);
-      const uint32_t direct_first = far_origin ? T.wide_first : T.always_first;
-      const uint32_t direct_end = T.always_first + T.always_count;
-      for(uint32_t j = direct_first; j < direct_end; ++j) {
-        bz_cull_rec c;
-        uint32_t patch = bz_load_cull(T.leaf, j, c);
-        float cosine, distance;
-        if(bz_stage_a(c, s, d, true, cosine, distance)) {
-          bz_push_candidate(sm, T, t, patch, s, d, ikey, ihit, ipatch, c_a, c_b);
-        }
-      }
-      c_a += direct_end - direct_first;
-    }
     __syncthreads();
 
     // ---- 3. stage B: dense passes over the survivor queue, then over the follow-hop queue ----
@@ -538,7 +472,7 @@ __global__ void bz_fma_probe_kernel(float *sink, uint32_t iters) {
 extern "C++" cudaError_t bz_launch_trace(int job, bool brute, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream) {
 #define BZ_LAUNCH(JOBV) \
   if(brute) { bz_trace_kernel<JOBV, true><<<grid, BZ_NT, 0, stream>>>(tables, desc); } \
-  else { bz_trace_kernel<JOBV, false><<<grid, BZ_NT, 0, stream>>>(tables, desc); }
+  else { return cudaErrorInvalidValue; }     /* BZ_MODE_CULLED runs bz_warp_trace_kernel (bz_trace.cu) */
   if(job == BZ_JOB_RENDER) { BZ_LAUNCH(BZ_JOB_RENDER) }
   else if(job == BZ_JOB_REFRACT) { BZ_LAUNCH(BZ_JOB_REFRACT) }
   else { BZ_LAUNCH(BZ_JOB_INTERSECT) }

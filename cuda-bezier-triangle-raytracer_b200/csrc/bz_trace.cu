@@ -1,0 +1,475 @@
+// bz_trace.cu -- the persistent, warp-scheduled intersect/refract kernel (BZ_MODE_CULLED) for sm_100a.
+//
+// One kernel, bz_warp_trace_kernel<JOB>, serves the three entry points of the C ABI:
+//   JOB_RENDER     K1 ray generation + bounce loop around BezierLens::refract + K3 background shading
+//   JOB_REFRACT    BezierLens::refract over a ray batch   (reference/bezierLens.cpp:4-34)
+//   JOB_INTERSECT  BezierMesh::intersect over a ray batch (reference/bezierMesh.cpp:206-227)
+//
+// Every WARP is its own scheduler: it owns a pool of BZ_SLOTS = 32 * BZ_GROUPS ray slots and two work queues in
+// shared memory and never meets another warp at a barrier.  One pass of its loop is one refract() call for every live
+// slot:
+//   refill     dead slots take the next primary-ray indices from a global counter (one atomic per warp and group);
+//              live rays stay where they are, so the pool stays compacted across bounces
+//   walk       per lane, the cull hierarchy in depth-first order with skip links (no stack): boxes of the flat
+//              underlying triangles, conservative slab test; leaf hits push (slot, leaf record) pairs to queue A
+//   stage A    queue A is consumed 32 pairs at a time: plane hit, self-hit gate, barycentric inside test
+//              (bezierTriangle.cpp:124-131); survivors go to queue B
+//   stage B    queue B is consumed 32 candidates at a time, whatever slot they belong to: bracket + 4 root-search steps
+//              (cpp:132-194); follow-side results are appended to queue B as one-hop candidates (bezierMesh.cpp:213-217);
+//              the nearest hit per slot is a 64-bit shared-memory atomicMin on (distance, loop index) -- the reference's
+//              "first strictly smaller distance wins" (bezierMesh.cpp:220)
+//   resolve    per slot: Snell refraction, expected-side check, next bounce or shading
+// Which of walk / stage A / stage B runs next is decided by queue levels, so the two stages always run on full
+// 32-lane batches except when a pass runs dry.
+// Compiled with -fmad=false (see bz_math.cuh); the box tests use explicit FMAs, they only have to be conservative.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "bz_device.h"
+#include "bz_math.cuh"
+
+#ifndef BZ_GROUPS
+#define BZ_GROUPS    2
+#endif
+#define BZ_WARPS     4
+#define BZ_SLOTS     (32 * BZ_GROUPS)
+#define BZ_QA_CAP    192
+#define BZ_QB_CAP    160
+#define BZ_LEAF_PUSH BZ_LEAF_MAX // upper bound of pairs one lane pushes in one walk step
+#define BZ_KEY_NONE  0xffffffffffffffffull
+#define BZ_NSTAT     9
+#define BZ_END       0xffffffffu
+
+struct bz_warp_pool {
+  float              ray[6][BZ_SLOTS];       // start xyz, dir xyz
+  unsigned long long best[BZ_SLOTS];         // (distance key, loop index) of the nearest hit of this pass
+  float              pay[11][BZ_SLOTS];      // point 3, normal 3, cos, bary 3, evaluated patch
+  uint32_t           id_lo[BZ_SLOTS];        // RENDER: local pixel index; batch jobs: ray index
+  uint32_t           id_hi[BZ_SLOTS];
+  uint32_t           state[BZ_SLOTS];        // bit 0 live, bits 1-2 expected status, bits 4.. crossings so far
+  uint32_t           qa_leaf[BZ_QA_CAP];     // queue A: record index in the `leaf` table
+  uint32_t           qb_patch[BZ_QB_CAP];    // queue B: patch to evaluate
+  uint32_t           qb_loop[BZ_QB_CAP];     //          loop index of the candidate (the originating patch for a hop)
+  uint8_t            qa_slot[BZ_QA_CAP];
+  uint8_t            qb_slot[BZ_QB_CAP];     //          slot | 0x80 for a first-level candidate (inside test applies, may hop)
+  uint32_t           qa_n, qb_n;
+};
+
+static_assert(BZ_SLOTS <= 128, "queue entries keep the slot in 7 bits");
+static_assert(BZ_QA_CAP >= 32 * BZ_LEAF_PUSH + 64 && BZ_QA_CAP <= 255 + 1 && BZ_QB_CAP >= 96, "queue thresholds");
+
+__device__ __forceinline__ void bzw_unpack_cull(const float4 *p, bz_cull_rec &c, uint32_t &index) {
+  float4 r0 = __ldg(p), r1 = __ldg(p + 1), r2 = __ldg(p + 2), r3 = __ldg(p + 3);
+  c.n = bz_v(r0.x, r0.y, r0.z); c.k = r0.w;
+  c.b0 = bz_v(r1.x, r1.y, r1.z); c.h_in = r1.w;
+  c.b1 = bz_v(r2.x, r2.y, r2.z); c.h_out = r2.w;
+  c.b2 = bz_v(r3.x, r3.y, r3.z);
+  index = __float_as_uint(r3.w);
+}
+
+__device__ __forceinline__ void bzw_load_newton(const float4 *p, bz_newton_rec &t) {
+  float w[48];
+#pragma unroll
+  for(int i = 0; i < BZ_NEWTON_F4; ++i) {
+    float4 r = __ldg(p + i);
+    w[4 * i] = r.x; w[4 * i + 1] = r.y; w[4 * i + 2] = r.z; w[4 * i + 3] = r.w;
+  }
+#pragma unroll
+  for(int i = 0; i < 10; ++i) { t.cp[i] = bz_v(w[3 * i], w[3 * i + 1], w[3 * i + 2]); }
+  t.dir_b = bz_v(w[30], w[31], w[32]);
+#pragma unroll
+  for(int i = 0; i < 3; ++i) {
+    t.div_n[i] = bz_v(w[33 + 4 * i], w[34 + 4 * i], w[35 + 4 * i]);
+    t.div_k[i] = w[36 + 4 * i];
+    t.nb[i] = __float_as_uint(w[45 + i]);
+  }
+}
+
+// K1: primary ray of sample (px, py, sx, sy); definitions in include/bz_capi.h (bz_camera).
+__device__ __forceinline__ void bzw_primary_ray(const bz_camera &cam, uint32_t px, uint32_t py, uint32_t sx, uint32_t sy, bzv3 &start, bzv3 &dir) {
+  float strata = (float)cam.strata;
+  float fu = (float)px + ((float)sx + 0.5f) / strata;
+  float fv = (float)py + ((float)sy + 0.5f) / strata;
+  float a = (fu * (2.0f / (float)cam.width) - 1.0f) * cam.half_w;
+  float b = (1.0f - fv * (2.0f / (float)cam.height)) * cam.half_h;
+  bzv3 offset = bz_v(cam.right[0] * a + cam.up[0] * b, cam.right[1] * a + cam.up[1] * b, cam.right[2] * a + cam.up[2] * b);
+  bzv3 raw;
+  if(cam.ortho != 0u) {
+    start = bz_v(cam.eye[0] + offset.x, cam.eye[1] + offset.y, cam.eye[2] + offset.z);
+    raw = bz_v(cam.forward[0], cam.forward[1], cam.forward[2]);
+  }
+  else {
+    start = bz_v(cam.eye[0], cam.eye[1], cam.eye[2]);
+    raw = bz_v(cam.forward[0] + offset.x, cam.forward[1] + offset.y, cam.forward[2] + offset.z);
+  }
+  dir = bz_normalized(raw);    // Ray::Ray, 3dGeomUtil.h:176-178
+}
+
+// K3: checker on the background plane, Plane::intersect semantics (3dGeomUtil.h:279-296).
+__device__ __forceinline__ uint32_t bzw_shade_background(const bz_scene &sc, const bzv3 &start, const bzv3 &dir) {
+  bzv3 n = bz_v(sc.bg_plane[0], sc.bg_plane[1], sc.bg_plane[2]);
+  float cosine = bz_dot(dir, n);
+  if(!(fabsf(cosine) >= BZ_PLANE_EPSILON)) { return sc.value_lost; }
+  float distance = (sc.bg_plane[3] - bz_dot(n, start)) / cosine;
+  if(!(distance > 0.0f)) { return sc.value_lost; }
+  bzv3 p = bz_v(start.x + distance * dir.x, start.y + distance * dir.y, start.z + distance * dir.z);
+  float ca = floorf(bz_dot(p, bz_v(sc.bg_axis_a[0], sc.bg_axis_a[1], sc.bg_axis_a[2])) / sc.cell);
+  float cb = floorf(bz_dot(p, bz_v(sc.bg_axis_b[0], sc.bg_axis_b[1], sc.bg_axis_b[2])) / sc.cell);
+  float pa = fabsf(fmodf(ca, 2.0f));
+  float pb = fabsf(fmodf(cb, 2.0f));
+  return (pa != pb) ? sc.value_bright : sc.value_dark;
+}
+
+__device__ __forceinline__ unsigned long long bzw_make_key(float distance, uint32_t loop_index) {
+  return ((unsigned long long)bz_float_key(distance) << 32) | (unsigned long long)loop_index;
+}
+
+__device__ __forceinline__ float bzw_key_distance(unsigned long long key) {
+  uint32_t k = (uint32_t)(key >> 32);
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+template<int JOB>
+__global__ void __launch_bounds__(32 * BZ_WARPS) bz_warp_trace_kernel(const bz_tables T, const bz_job J) {
+  __shared__ bz_warp_pool pools[BZ_WARPS];
+  bz_warp_pool &P = pools[threadIdx.x >> 5];
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t spp = J.camera.strata * J.camera.strata;
+  const uint32_t direct_end = T.always_first + T.always_count;
+  unsigned long long c_primary = 0ull, c_calls = 0ull, c_a = 0ull, c_nodes = 0ull;
+  uint32_t c_b = 0u, c_snell = 0u, c_enter = 0u, c_exit = 0u, c_lost = 0u;
+  bool exhausted = false;                    // warp-uniform: the global ray counter has run past the end
+
+#pragma unroll
+  for(int g = 0; g < BZ_GROUPS; ++g) { P.state[g * 32 + lane] = 0u; }
+  if(lane == 0u) { P.qa_n = 0u; P.qb_n = 0u; }
+  __syncwarp();
+
+  for(;;) {
+    // ================= one pass: one refract() call for every live slot =================
+    int group = 0;                           // warp-uniform: group whose walk is in progress; BZ_GROUPS = all walked
+    bool group_ready = false;                // warp-uniform: refill of `group` done, walk state valid
+    bool any_live = false;                   // warp-uniform
+    uint32_t node = BZ_END, direct = BZ_END; // per lane: walk state of the current group
+
+    for(;;) {
+      __syncwarp();
+      const uint32_t qa = P.qa_n, qb = P.qb_n;
+      __syncwarp();
+      const bool walked = (group == BZ_GROUPS);
+      int action;                            // warp-uniform: 0 walk, 1 stage A batch, 2 stage B batch, 3 pass complete
+      if(qb > BZ_QB_CAP - 64u) { action = 2; }
+      else if(qa > BZ_QA_CAP - 32u * BZ_LEAF_PUSH || (walked && qa != 0u)) { action = 1; }
+      else if(!walked) { action = 0; }
+      else if(qb != 0u) { action = 2; }
+      else { action = 3; }
+      if(action == 3) { break; }
+
+      if(action == 0) {
+        const uint32_t slot = (uint32_t)group * 32u + lane;
+        if(!group_ready) {
+          // ---- refill: dead slots of this group take the next primary rays ----
+          uint32_t st = P.state[slot];
+          bool live = (st & 1u) != 0u;
+          const uint32_t need = __ballot_sync(0xffffffffu, !live);
+          if(need != 0u && !exhausted) {
+            unsigned long long base = 0ull;
+            const int leader = __ffs(need) - 1;
+            if((int)lane == leader) { base = atomicAdd(J.next_ray, (unsigned long long)__popc(need)); }
+            base = __shfl_sync(0xffffffffu, base, leader);
+            exhausted = (base + (unsigned long long)__popc(need) >= J.ray_count);
+            if(!live) {
+              const unsigned long long id = base + (unsigned long long)__popc(need & ((1u << lane) - 1u));
+              if(id < J.ray_count) {
+                bzv3 s, d;
+                uint32_t expected = BZ_STATUS_INSIDE;
+                if(JOB == BZ_JOB_RENDER) {
+                  const uint32_t pixel = (uint32_t)(id / spp);
+                  const uint32_t sample = (uint32_t)(id - (unsigned long long)pixel * spp);
+                  const uint32_t row = pixel / J.camera.width;
+                  const uint32_t px = pixel - row * J.camera.width;
+                  const uint32_t py = (J.stripe_rows == 0u) ? J.row0 + row
+                                    : ((row / J.stripe_rows) * J.stripe_ranks + J.stripe_rank) * J.stripe_rows + row % J.stripe_rows;
+                  bzw_primary_ray(J.camera, px, py, sample % J.camera.strata, sample / J.camera.strata, s, d);
+                  P.id_lo[slot] = pixel;
+                }
+                else {
+                  s = bz_v(J.in_start[id * 3u], J.in_start[id * 3u + 1u], J.in_start[id * 3u + 2u]);
+                  d = bz_v(J.in_dir[id * 3u], J.in_dir[id * 3u + 1u], J.in_dir[id * 3u + 2u]);
+                  expected = (JOB == BZ_JOB_REFRACT) ? (J.in_expected[id] & 3u) : 0u;
+                  P.id_lo[slot] = (uint32_t)id;
+                  P.id_hi[slot] = (uint32_t)(id >> 32);
+                }
+                P.ray[0][slot] = s.x; P.ray[1][slot] = s.y; P.ray[2][slot] = s.z;
+                P.ray[3][slot] = d.x; P.ray[4][slot] = d.y; P.ray[5][slot] = d.z;
+                st = 1u | (expected << 1);
+                P.state[slot] = st;
+                live = true;
+                ++c_primary;
+              }
+            }
+          }
+          P.best[slot] = BZ_KEY_NONE;
+          any_live = any_live || (__ballot_sync(0xffffffffu, live) != 0u);
+          if(live) {
+            const float l1 = fabsf(P.ray[0][slot]) + fabsf(P.ray[1][slot]) + fabsf(P.ray[2][slot]);
+            direct = (l1 <= T.origin_limit) ? T.always_first : T.wide_first;     // far origins also test the wide segment
+            if(direct >= direct_end) { direct = BZ_END; }
+            node = (T.node_count != 0u) ? 0u : BZ_END;
+            ++c_calls;
+          }
+          else {
+            direct = BZ_END;
+            node = BZ_END;
+          }
+          group_ready = true;
+        }
+        // ---- walk: records outside the hierarchy first, then the hierarchy, until done or queue A fills up ----
+        {
+          const float sx = P.ray[0][slot], sy = P.ray[1][slot], sz = P.ray[2][slot];
+          const float dx = P.ray[3][slot], dy = P.ray[4][slot], dz = P.ray[5][slot];
+          // per-ray slack of the box tests: covers the rounding of stage A's in-plane point and barycentrics for
+          // patches whose conditioning is <= 16 (host/bz_bvh.cpp)
+          const float slack = 3.0517578125e-05f * (fabsf(sx) + fabsf(sy) + fabsf(sz) + 2.0f * T.extent);
+          const float ix = (fabsf(dx) > 1e-20f) ? 1.0f / dx : copysignf(1e20f, dx);
+          const float iy = (fabsf(dy) > 1e-20f) ? 1.0f / dy : copysignf(1e20f, dy);
+          const float iz = (fabsf(dz) > 1e-20f) ? 1.0f / dz : copysignf(1e20f, dz);
+          const float ax_lo = -(sx + slack) * ix, ax_hi = -(sx - slack) * ix;
+          const float ay_lo = -(sy + slack) * iy, ay_hi = -(sy - slack) * iy;
+          const float az_lo = -(sz + slack) * iz, az_hi = -(sz - slack) * iz;
+          uint32_t room = BZ_QA_CAP - qa;      // warp-uniform lower bound of the free entries of queue A
+          for(;;) {
+            const bool busy = (direct != BZ_END) || (node != BZ_END);
+            if(__ballot_sync(0xffffffffu, busy) == 0u) {
+              group_ready = false;
+              ++group;
+              break;
+            }
+            if(room < 32u * BZ_LEAF_PUSH) { break; }
+            uint32_t first = 0u, count = 0u;
+            if(direct != BZ_END) {
+              first = direct;
+              count = 1u;
+              ++direct;
+              if(direct >= direct_end) { direct = BZ_END; }
+            }
+            else if(node != BZ_END) {
+              const float4 lo = __ldg(T.nodes + (size_t)node * BZ_NODE_F4);
+              const float4 hi = __ldg(T.nodes + (size_t)node * BZ_NODE_F4 + 1);
+              ++c_nodes;
+              const float x0 = __fmaf_rn(lo.x, ix, ax_lo), x1 = __fmaf_rn(hi.x, ix, ax_hi);
+              const float y0 = __fmaf_rn(lo.y, iy, ay_lo), y1 = __fmaf_rn(hi.y, iy, ay_hi);
+              const float z0 = __fmaf_rn(lo.z, iz, az_lo), z1 = __fmaf_rn(hi.z, iz, az_hi);
+              const float tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+              const float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+              const bool hit = (tnear <= tfar * 1.000001f);
+              const uint32_t code = __float_as_uint(hi.w);
+              if(hit && code != 0u) { first = code >> 3; count = code & 7u; }
+              node = (hit && code == 0u) ? node + 1u : __float_as_uint(lo.w);
+              if(node >= T.node_count) { node = BZ_END; }
+            }
+            if(count != 0u) {
+              const uint32_t at = atomicAdd(&P.qa_n, count);
+              for(uint32_t j = 0u; j < count; ++j) {
+                P.qa_leaf[at + j] = first + j;
+                P.qa_slot[at + j] = (uint8_t)slot;
+              }
+            }
+            room -= (uint32_t)__popc(__ballot_sync(0xffffffffu, count != 0u)) * BZ_LEAF_PUSH;
+          }
+        }
+        continue;
+      }
+
+      if(action == 1) {
+        // ---- stage A on (up to) 32 pairs from the tail of queue A ----
+        const uint32_t n = min(qa, 32u);
+        const uint32_t q = qa - n + lane;
+        if(lane == 0u) { P.qa_n = qa - n; }
+        if(lane < n) {
+          const uint32_t slot = P.qa_slot[q];
+          bz_cull_rec c;
+          uint32_t patch;
+          bzw_unpack_cull(T.leaf + (size_t)P.qa_leaf[q] * BZ_CULL_F4, c, patch);
+          const bzv3 s = bz_v(P.ray[0][slot], P.ray[1][slot], P.ray[2][slot]);
+          const bzv3 d = bz_v(P.ray[3][slot], P.ray[4][slot], P.ray[5][slot]);
+          float cosine, distance;
+          ++c_a;
+          if(bz_stage_a(c, s, d, true, cosine, distance)) {
+            const uint32_t at = atomicAdd(&P.qb_n, 1u);
+            P.qb_patch[at] = patch;
+            P.qb_loop[at] = patch;
+            P.qb_slot[at] = (uint8_t)(slot | 0x80u);
+          }
+        }
+        continue;
+      }
+
+      // ---- action 2: stage B on (up to) 32 candidates from the tail of queue B ----
+      {
+        const uint32_t n = min(qb, 32u);
+        const uint32_t q = qb - n + lane;
+        if(lane == 0u) { P.qb_n = qb - n; }
+        uint32_t slot = 0u, patch = 0u, loop = 0u;
+        bool first_level = false;
+        if(lane < n) {
+          const uint32_t packed = P.qb_slot[q];
+          slot = packed & 0x7fu;
+          first_level = (packed & 0x80u) != 0u;
+          patch = P.qb_patch[q];
+          loop = P.qb_loop[q];
+        }
+        __syncwarp();                          // the entries are read before anyone appends a hop
+        unsigned long long key = BZ_KEY_NONE;
+        bz_hit hit;
+        hit.what = BZ_MISS;
+        if(lane < n) {
+          bz_cull_rec c;
+          uint32_t index;
+          bzw_unpack_cull(T.cull + (size_t)patch * BZ_CULL_F4, c, index);
+          const bzv3 s = bz_v(P.ray[0][slot], P.ray[1][slot], P.ray[2][slot]);
+          const bzv3 d = bz_v(P.ray[3][slot], P.ray[4][slot], P.ray[5][slot]);
+          float cosine, distance;
+          if(!first_level) { ++c_a; }
+          if(bz_stage_a(c, s, d, first_level, cosine, distance)) {
+            bz_newton_rec t;
+            bzw_load_newton(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
+            bz_stage_b(c, t, s, d, cosine, distance, hit);
+            ++c_b;
+            if(hit.what <= BZ_FOLLOW2) {
+              if(first_level) {                // one hop, no recursion (bezierMesh.cpp:213-217)
+                const uint32_t at = atomicAdd(&P.qb_n, 1u);
+                P.qb_patch[at] = t.nb[hit.what];
+                P.qb_loop[at] = loop;
+                P.qb_slot[at] = (uint8_t)slot;
+              }
+            }
+            else if(hit.what == BZ_HIT && hit.distance < 3.402823466e+38f) {      // bezierMesh.cpp:209, 220
+              key = bzw_make_key(hit.distance, loop);
+              atomicMin(&P.best[slot], key);
+            }
+          }
+        }
+        __syncwarp();
+        if(key != BZ_KEY_NONE && P.best[slot] == key) {
+          P.pay[0][slot] = hit.point.x;  P.pay[1][slot] = hit.point.y;  P.pay[2][slot] = hit.point.z;
+          P.pay[3][slot] = hit.normal.x; P.pay[4][slot] = hit.normal.y; P.pay[5][slot] = hit.normal.z;
+          P.pay[6][slot] = hit.cos_incidence;
+          P.pay[7][slot] = hit.bary.x;   P.pay[8][slot] = hit.bary.y;   P.pay[9][slot] = hit.bary.z;
+          P.pay[10][slot] = __uint_as_float(patch);
+        }
+      }
+    }
+    if(!any_live) { break; }
+
+    // ================= resolve: nearest hit -> Snell -> expected-side check -> next bounce or finish =================
+    __syncwarp();
+#pragma unroll
+    for(int g = 0; g < BZ_GROUPS; ++g) {
+      const uint32_t slot = (uint32_t)g * 32u + lane;
+      const uint32_t st = P.state[slot];
+      if((st & 1u) == 0u) { continue; }
+      uint32_t expected = (st >> 1) & 3u;
+      uint32_t crossings = st >> 4;
+      const unsigned long long key = P.best[slot];
+      const bool found = (key != BZ_KEY_NONE);
+      bzv3 s = bz_v(P.ray[0][slot], P.ray[1][slot], P.ray[2][slot]);
+      bzv3 d = bz_v(P.ray[3][slot], P.ray[4][slot], P.ray[5][slot]);
+      bz_hit hit;
+      hit.point = bz_v(P.pay[0][slot], P.pay[1][slot], P.pay[2][slot]);
+      hit.normal = bz_v(P.pay[3][slot], P.pay[4][slot], P.pay[5][slot]);
+      hit.cos_incidence = P.pay[6][slot];
+      hit.bary = bz_v(P.pay[7][slot], P.pay[8][slot], P.pay[9][slot]);
+      const uint32_t patch = __float_as_uint(P.pay[10][slot]);
+      bool live = true;
+      if(JOB == BZ_JOB_INTERSECT) {
+        const unsigned long long ray_id = ((unsigned long long)P.id_hi[slot] << 32) | P.id_lo[slot];
+        J.out_status[ray_id] = found ? BZ_WHAT_INTERSECT : BZ_WHAT_NONE;
+        if(J.out_patch != nullptr) { J.out_patch[ray_id] = found ? patch : BZ_NO_PATCH; }
+        if(J.out_distance != nullptr) { J.out_distance[ray_id] = found ? bzw_key_distance(key) : 0.0f; }
+        if(J.out_cos != nullptr) { J.out_cos[ray_id] = found ? hit.cos_incidence : 0.0f; }
+        if(J.out_point != nullptr) {
+          J.out_point[ray_id * 3u] = found ? hit.point.x : 0.0f; J.out_point[ray_id * 3u + 1u] = found ? hit.point.y : 0.0f; J.out_point[ray_id * 3u + 2u] = found ? hit.point.z : 0.0f;
+        }
+        if(J.out_normal != nullptr) {
+          J.out_normal[ray_id * 3u] = found ? hit.normal.x : 0.0f; J.out_normal[ray_id * 3u + 1u] = found ? hit.normal.y : 0.0f; J.out_normal[ray_id * 3u + 2u] = found ? hit.normal.z : 0.0f;
+        }
+        if(J.out_bary != nullptr) {
+          J.out_bary[ray_id * 3u] = found ? hit.bary.x : 0.0f; J.out_bary[ray_id * 3u + 1u] = found ? hit.bary.y : 0.0f; J.out_bary[ray_id * 3u + 2u] = found ? hit.bary.z : 0.0f;
+        }
+        live = false;
+      }
+      else {
+        uint32_t status = BZ_STATUS_NONE;
+        bzv3 refracted = d;
+        if(found) {
+          status = bz_snell(T.ri, hit.cos_incidence, hit.normal, refracted);
+          ++c_snell;
+        }
+        status = (status == expected) ? status : BZ_STATUS_NONE;
+        if(status != BZ_STATUS_NONE) {
+          s = hit.point;
+          d = refracted;
+          if(status == BZ_STATUS_INSIDE) { ++c_enter; } else { ++c_exit; }
+        }
+        if(JOB == BZ_JOB_REFRACT) {
+          const unsigned long long ray_id = ((unsigned long long)P.id_hi[slot] << 32) | P.id_lo[slot];
+          J.out_start[ray_id * 3u] = s.x; J.out_start[ray_id * 3u + 1u] = s.y; J.out_start[ray_id * 3u + 2u] = s.z;
+          J.out_dir[ray_id * 3u] = d.x; J.out_dir[ray_id * 3u + 1u] = d.y; J.out_dir[ray_id * 3u + 2u] = d.z;
+          J.out_status[ray_id] = status;
+          if(J.out_patch != nullptr) { J.out_patch[ray_id] = found ? patch : BZ_NO_PATCH; }
+          live = false;
+        }
+        else {
+          bool done = (status == BZ_STATUS_NONE);
+          if(!done) {
+            expected = (expected == BZ_STATUS_INSIDE) ? BZ_STATUS_OUTSIDE : BZ_STATUS_INSIDE;
+            ++crossings;
+            done = (crossings >= J.scene.max_crossings);
+          }
+          if(done) {
+            uint32_t value;
+            if(expected == BZ_STATUS_INSIDE) {      // the ray is in air: it reaches the background
+              value = bzw_shade_background(J.scene, s, d);
+            }
+            else {                                  // entered and never left
+              value = J.scene.value_lost;
+              ++c_lost;
+            }
+            atomicAdd(J.accum + P.id_lo[slot], value);
+            live = false;
+          }
+          else {
+            P.ray[0][slot] = s.x; P.ray[1][slot] = s.y; P.ray[2][slot] = s.z;
+            P.ray[3][slot] = d.x; P.ray[4][slot] = d.y; P.ray[5][slot] = d.z;
+          }
+        }
+      }
+      P.state[slot] = live ? (1u | (expected << 1) | (crossings << 4)) : 0u;
+    }
+  }
+
+  // ---- work counters: warp reduce, one atomic per warp and counter ----
+  if(J.stats != nullptr) {
+    unsigned long long v[BZ_NSTAT] = { c_primary, c_calls, c_a, (unsigned long long)c_b, (unsigned long long)c_snell,
+                                       (unsigned long long)c_enter, (unsigned long long)c_exit, (unsigned long long)c_lost, c_nodes };
+#pragma unroll
+    for(int i = 0; i < BZ_NSTAT; ++i) {
+      unsigned long long x = v[i];
+      for(int o = 16; o > 0; o >>= 1) { x += __shfl_down_sync(0xffffffffu, x, o); }
+      if(lane == 0u && x != 0ull) { atomicAdd(J.stats + i, x); }
+    }
+  }
+}
+
+cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream) {
+  if(job == BZ_JOB_RENDER) { bz_warp_trace_kernel<BZ_JOB_RENDER><<<grid, 32 * BZ_WARPS, 0, stream>>>(tables, desc); }
+  else if(job == BZ_JOB_REFRACT) { bz_warp_trace_kernel<BZ_JOB_REFRACT><<<grid, 32 * BZ_WARPS, 0, stream>>>(tables, desc); }
+  else { bz_warp_trace_kernel<BZ_JOB_INTERSECT><<<grid, 32 * BZ_WARPS, 0, stream>>>(tables, desc); }
+  return cudaGetLastError();
+}
+
+// resident CTAs per SM of the render instantiation (the persistent grid is sized from it), rays per CTA pass
+cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta) {
+  *out_rays_per_cta = BZ_WARPS * BZ_SLOTS;
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(out_ctas_per_sm, bz_warp_trace_kernel<BZ_JOB_RENDER>, 32 * BZ_WARPS, 0);
+}

@@ -22,6 +22,10 @@
 #include <vector>
 #include "bz_bvh.h"
 
+#ifndef BZ_BVH_LEAF_MAX
+#define BZ_BVH_LEAF_MAX 2     // = BZ_LEAF_MAX of csrc/bz_device.h (bz_capi.cu checks it)
+#endif
+
 namespace {
 
 struct Box {
@@ -43,6 +47,7 @@ struct Binary {
 };
 
 constexpr int cBins = 16;
+constexpr uint32_t cLeafMax = BZ_BVH_LEAF_MAX;   // <= 7 (3 bits in the leaf code)
 constexpr double cKappaLimit = 16.0;
 constexpr double cKappaWideLimit = 65536.0;
 constexpr double cSlackUnit = 1.9073486328125e-06;     // 2^-19; the kernel's per-ray slack is cKappaLimit * cSlackUnit * (|s|_1 + 2 extent)
@@ -68,7 +73,7 @@ struct Builder {
     node.count = end - begin;
     int const index = static_cast<int>(nodes.size());
     nodes.push_back(node);
-    if(end - begin <= 3u) { return index; }
+    if(end - begin <= cLeafMax) { return index; }
 
     uint32_t mid = begin;
     bool split = false;
@@ -128,15 +133,6 @@ struct Builder {
     return index;
   }
 };
-
-void writeChild(std::vector<float> &out, size_t node, int slot, const Box &box, int32_t code) {
-  float *p = out.data() + node * 32u;
-  p[0 + slot] = box.lo[0];  p[4 + slot] = box.hi[0];
-  p[8 + slot] = box.lo[1];  p[12 + slot] = box.hi[1];
-  p[16 + slot] = box.lo[2]; p[20 + slot] = box.hi[2];
-  static_assert(sizeof(float) == sizeof(int32_t), "child codes are stored in float lanes");
-  std::memcpy(p + 24 + slot, &code, sizeof(code));
-}
 
 }
 
@@ -214,49 +210,43 @@ void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out) {
   out.order.resize(n);
   for(uint32_t i = 0u; i < n; ++i) { out.order[i] = prims[b.order[i]]; }
 
-  // collapse the binary tree into 4-wide nodes: repeatedly open the inner child with the largest box
-  struct Pending { int binary; size_t wide; uint32_t depth; };
-  std::vector<Pending> todo;
-  auto emit = [&](int binary, uint32_t depth) -> size_t {
-    size_t const at = out.nodes.size() / 32u;
-    out.nodes.resize(out.nodes.size() + 32u, 0.0f);
-    todo.push_back({ binary, at, depth });
-    return at;
-  };
-  emit(root, 1u);
+  // flatten in depth-first order with skip links: node i is followed by its first child (inner node) or by the next
+  // subtree (leaf); link = index of the first node after the subtree of i, taken when the box is missed
+  struct Frame { int binary; size_t flat; uint32_t depth; int stage; };
+  std::vector<Frame> todo;
+  todo.push_back({ root, 0u, 1u, 0 });
   while(!todo.empty()) {
-    Pending const job = todo.back();
-    todo.pop_back();
-    out.depth = std::max(out.depth, job.depth);
-    std::vector<int> kids;
-    if(b.nodes[job.binary].left < 0) {
-      kids.push_back(job.binary);           // the whole tree is one leaf
-    }
-    else {
-      kids.push_back(b.nodes[job.binary].left);
-      kids.push_back(b.nodes[job.binary].right);
-      while(kids.size() < 4u) {
-        int pick = -1;
-        double area = -1.0;
-        for(size_t k = 0u; k < kids.size(); ++k) {
-          if(b.nodes[kids[k]].left >= 0 && b.nodes[kids[k]].box.area() > area) { area = b.nodes[kids[k]].box.area(); pick = static_cast<int>(k); }
-        }
-        if(pick < 0) { break; }
-        int const opened = kids[pick];
-        kids[pick] = b.nodes[opened].left;
-        kids.push_back(b.nodes[opened].right);
-      }
-    }
-    for(size_t k = 0u; k < kids.size(); ++k) {
-      Binary const &kid = b.nodes[kids[k]];
-      int32_t code;
-      if(kid.left < 0) {
-        code = ~static_cast<int32_t>((kid.first << 3u) | kid.count);
+    Frame &job = todo.back();
+    Binary const &bin = b.nodes[job.binary];
+    if(job.stage == 0) {
+      job.flat = out.nodes.size() / 8u;
+      out.nodes.resize(out.nodes.size() + 8u, 0.0f);
+      float *p = out.nodes.data() + job.flat * 8u;
+      p[0] = bin.box.lo[0]; p[1] = bin.box.lo[1]; p[2] = bin.box.lo[2];
+      p[4] = bin.box.hi[0]; p[5] = bin.box.hi[1]; p[6] = bin.box.hi[2];
+      out.depth = std::max(out.depth, job.depth);
+      if(bin.left < 0) {
+        uint32_t const code = (bin.first << 3u) | bin.count;      // never 0: count >= 1
+        std::memcpy(p + 7, &code, sizeof(code));
+        job.stage = 3;
       }
       else {
-        code = static_cast<int32_t>(emit(kids[k], job.depth + 1u));
+        job.stage = 1;
+        int const child = bin.left;
+        uint32_t const depth = job.depth + 1u;
+        todo.push_back({ child, 0u, depth, 0 });                 // invalidates `job`
       }
-      writeChild(out.nodes, job.wide, static_cast<int>(k), kid.box, code);
+    }
+    else if(job.stage == 1) {
+      job.stage = 3;
+      int const child = bin.right;
+      uint32_t const depth = job.depth + 1u;
+      todo.push_back({ child, 0u, depth, 0 });
+    }
+    else {
+      uint32_t const link = static_cast<uint32_t>(out.nodes.size() / 8u);
+      std::memcpy(out.nodes.data() + job.flat * 8u + 3u, &link, sizeof(link));
+      todo.pop_back();
     }
   }
 }

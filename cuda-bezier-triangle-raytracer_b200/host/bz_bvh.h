@@ -7,14 +7,14 @@
 #include "bz_capi.h"
 
 struct bz_bvh {
-  std::vector<float>    nodes;    // 32 floats per 4-wide node, layout in csrc/bz_device.h
+  std::vector<float>    nodes;    // 8 floats per node in depth-first order: lo.xyz, skip link, hi.xyz, leaf code (csrc/bz_device.h)
   std::vector<uint32_t> order;    // leaf slot -> patch index
   std::vector<uint32_t> wide;     // ill-conditioned patches kept in the hierarchy with grown boxes; a ray whose origin has
                                   // |s|_1 > origin_limit tests them directly as well
   std::vector<uint32_t> always;   // patches outside the hierarchy, tested for every ray
   float                 extent;   // max |coordinate| of the flat triangles
   float                 origin_limit;
-  uint32_t              depth;    // levels of 4-wide nodes
+  uint32_t              depth;    // levels of the binary hierarchy
 };
 
 void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out);

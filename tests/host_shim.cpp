@@ -84,29 +84,26 @@ void shim_intersect_batch(const bz_patch *patches, uint32_t count, const float *
         alo[k] = -(o[k] + slack) * inv[k];
         ahi[k] = -(o[k] - slack) * inv[k];
       }
-      std::vector<int> stack;
-      if(!bvh.nodes.empty()) { stack.push_back(0); }
-      while(!stack.empty()) {
-        int node = stack.back();
-        stack.pop_back();
+      uint32_t const nodeCount = (uint32_t)(bvh.nodes.size() / 8u);
+      uint32_t node = 0u;
+      while(node < nodeCount) {                     // depth-first order with skip links, as the kernel walks it
         ++visited[1];
-        const float *p = bvh.nodes.data() + (size_t)node * 32u;
-        for(int k = 0; k < 4; ++k) {
-          int32_t child;
-          std::memcpy(&child, p + 24 + k, sizeof(child));
-          if(child == 0) { continue; }
-          float tnear = 0.0f, tfar = 3.0e38f;
-          for(int a = 0; a < 3; ++a) {
-            float t0 = std::fma(p[8 * a + k], inv[a], alo[a]), t1 = std::fma(p[8 * a + 4 + k], inv[a], ahi[a]);
-            tnear = std::fmax(tnear, std::fmin(t0, t1));
-            tfar = std::fmin(tfar, std::fmax(t0, t1));
-          }
-          if(!(tnear <= tfar * 1.000001f)) { continue; }
-          if(child > 0) { stack.push_back(child); continue; }
-          uint32_t code = (uint32_t)(~child);
+        const float *p = bvh.nodes.data() + (size_t)node * 8u;
+        uint32_t link, code;
+        std::memcpy(&link, p + 3, sizeof(link));
+        std::memcpy(&code, p + 7, sizeof(code));
+        float tnear = 0.0f, tfar = 3.0e38f;
+        for(int a = 0; a < 3; ++a) {
+          float t0 = std::fma(p[a], inv[a], alo[a]), t1 = std::fma(p[4 + a], inv[a], ahi[a]);
+          tnear = std::fmax(tnear, std::fmin(t0, t1));
+          tfar = std::fmin(tfar, std::fmax(t0, t1));
+        }
+        bool const hit = (tnear <= tfar * 1.000001f);
+        if(hit && code != 0u) {
           for(uint32_t j = 0u; j < (code & 7u); ++j) { candidate(patches, bvh.order[(code >> 3) + j], s, d, best); }
           visited[0] += (code & 7u);
         }
+        node = (hit && code == 0u) ? node + 1u : link;
       }
       if(!(std::fabs(s.x) + std::fabs(s.y) + std::fabs(s.z) <= bvh.origin_limit)) {
         for(uint32_t i : bvh.wide) { candidate(patches, i, s, d, best); }
@@ -142,7 +139,7 @@ uint32_t shim_snell(float ri, float cos_incidence, const float *normal, float *d
 void shim_bvh_info(const bz_patch *patches, uint32_t count, uint32_t *out) {
   bz_bvh bvh;
   bz_build_bvh(patches, count, bvh);
-  out[0] = (uint32_t)(bvh.nodes.size() / 32u);
+  out[0] = (uint32_t)(bvh.nodes.size() / 8u);
   out[1] = bvh.depth;
   out[2] = (uint32_t)bvh.always.size();
   out[3] = (uint32_t)bvh.order.size();
