@@ -28,11 +28,20 @@
 #include "bz_math.cuh"
 
 #ifndef BZ_GROUPS
-#define BZ_GROUPS    2
+#define BZ_GROUPS    1
 #endif
 #define BZ_WARPS     4
+#ifndef BZ_MIN_CTAS
+#define BZ_MIN_CTAS  5
+#endif
 #define BZ_SLOTS     (32 * BZ_GROUPS)
-#define BZ_QA_CAP    192
+#ifndef BZ_WALK_BURST
+#define BZ_WALK_BURST 4
+#endif
+//        // hierarchy steps per lane between two looks at the level of queue A
+#ifndef BZ_QA_CAP
+#define BZ_QA_CAP    512
+#endif
 #define BZ_QB_CAP    160
 #define BZ_LEAF_PUSH BZ_LEAF_MAX // upper bound of pairs one lane pushes in one walk step
 #define BZ_KEY_NONE  0xffffffffffffffffull
@@ -55,7 +64,7 @@ struct bz_warp_pool {
 };
 
 static_assert(BZ_SLOTS <= 128, "queue entries keep the slot in 7 bits");
-static_assert(BZ_QA_CAP >= 32 * BZ_LEAF_PUSH + 64 && BZ_QA_CAP <= 255 + 1 && BZ_QB_CAP >= 96, "queue thresholds");
+static_assert(BZ_QA_CAP >= 32 * BZ_LEAF_PUSH * BZ_WALK_BURST + 64 && BZ_QB_CAP >= 96, "queue thresholds");
 
 __device__ __forceinline__ void bzw_unpack_cull(const float4 *p, bz_cull_rec &c, uint32_t &index) {
   float4 r0 = __ldg(p), r1 = __ldg(p + 1), r2 = __ldg(p + 2), r3 = __ldg(p + 3);
@@ -129,7 +138,7 @@ __device__ __forceinline__ float bzw_key_distance(unsigned long long key) {
 }
 
 template<int JOB>
-__global__ void __launch_bounds__(32 * BZ_WARPS) bz_warp_trace_kernel(const bz_tables T, const bz_job J) {
+__global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kernel(const bz_tables T, const bz_job J) {
   __shared__ bz_warp_pool pools[BZ_WARPS];
   bz_warp_pool &P = pools[threadIdx.x >> 5];
   const uint32_t lane = threadIdx.x & 31u;
@@ -158,7 +167,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS) bz_warp_trace_kernel(const bz_t
       const bool walked = (group == BZ_GROUPS);
       int action;                            // warp-uniform: 0 walk, 1 stage A batch, 2 stage B batch, 3 pass complete
       if(qb > BZ_QB_CAP - 64u) { action = 2; }
-      else if(qa > BZ_QA_CAP - 32u * BZ_LEAF_PUSH || (walked && qa != 0u)) { action = 1; }
+      else if(qa > BZ_QA_CAP - 32u * BZ_LEAF_PUSH * BZ_WALK_BURST || (walked && qa != 0u)) { action = 1; }
       else if(!walked) { action = 0; }
       else if(qb != 0u) { action = 2; }
       else { action = 3; }
@@ -236,46 +245,57 @@ __global__ void __launch_bounds__(32 * BZ_WARPS) bz_warp_trace_kernel(const bz_t
           const float ax_lo = -(sx + slack) * ix, ax_hi = -(sx - slack) * ix;
           const float ay_lo = -(sy + slack) * iy, ay_hi = -(sy - slack) * iy;
           const float az_lo = -(sz + slack) * iz, az_hi = -(sz - slack) * iz;
+          // records outside the hierarchy (always segment; wide segment for far origins): one pair per lane and turn
           uint32_t room = BZ_QA_CAP - qa;      // warp-uniform lower bound of the free entries of queue A
-          for(;;) {
-            const bool busy = (direct != BZ_END) || (node != BZ_END);
-            if(__ballot_sync(0xffffffffu, busy) == 0u) {
+          bool paused = false;
+          while(__ballot_sync(0xffffffffu, direct != BZ_END) != 0u) {
+            if(room < 32u) { paused = true; break; }
+            if(direct != BZ_END) {
+              const uint32_t at = atomicAdd(&P.qa_n, 1u);
+              P.qa_leaf[at] = direct;
+              P.qa_slot[at] = (uint8_t)slot;
+              ++direct;
+              if(direct >= direct_end) { direct = BZ_END; }
+            }
+            room -= 32u;
+          }
+          // the hierarchy: BZ_WALK_BURST steps per lane between two looks at the queue level
+          uint32_t steps = 0u;
+          while(!paused) {
+#pragma unroll
+            for(int u = 0; u < BZ_WALK_BURST; ++u) {
+              if(node != BZ_END) {
+                const float4 lo = __ldg(T.nodes + (size_t)node * BZ_NODE_F4);
+                const float4 hi = __ldg(T.nodes + (size_t)node * BZ_NODE_F4 + 1);
+                ++steps;
+                const float x0 = __fmaf_rn(lo.x, ix, ax_lo), x1 = __fmaf_rn(hi.x, ix, ax_hi);
+                const float y0 = __fmaf_rn(lo.y, iy, ay_lo), y1 = __fmaf_rn(hi.y, iy, ay_hi);
+                const float z0 = __fmaf_rn(lo.z, iz, az_lo), z1 = __fmaf_rn(hi.z, iz, az_hi);
+                const float tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+                const float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+                const bool hit = (tnear <= tfar * 1.000001f);
+                const uint32_t code = __float_as_uint(hi.w);
+                if(hit && code != 0u) {            // leaf: its records go to queue A
+                  const uint32_t count = code & 7u;
+                  const uint32_t at = atomicAdd(&P.qa_n, count);
+                  for(uint32_t j = 0u; j < count; ++j) {
+                    P.qa_leaf[at + j] = (code >> 3) + j;
+                    P.qa_slot[at + j] = (uint8_t)slot;
+                  }
+                }
+                // inner node that was hit: its first child is the next node; otherwise skip the subtree (BZ_END after the last)
+                node = (hit && code == 0u) ? node + 1u : __float_as_uint(lo.w);
+              }
+            }
+            if(__ballot_sync(0xffffffffu, node != BZ_END) == 0u) {
               group_ready = false;
               ++group;
               break;
             }
-            if(room < 32u * BZ_LEAF_PUSH) { break; }
-            uint32_t first = 0u, count = 0u;
-            if(direct != BZ_END) {
-              first = direct;
-              count = 1u;
-              ++direct;
-              if(direct >= direct_end) { direct = BZ_END; }
-            }
-            else if(node != BZ_END) {
-              const float4 lo = __ldg(T.nodes + (size_t)node * BZ_NODE_F4);
-              const float4 hi = __ldg(T.nodes + (size_t)node * BZ_NODE_F4 + 1);
-              ++c_nodes;
-              const float x0 = __fmaf_rn(lo.x, ix, ax_lo), x1 = __fmaf_rn(hi.x, ix, ax_hi);
-              const float y0 = __fmaf_rn(lo.y, iy, ay_lo), y1 = __fmaf_rn(hi.y, iy, ay_hi);
-              const float z0 = __fmaf_rn(lo.z, iz, az_lo), z1 = __fmaf_rn(hi.z, iz, az_hi);
-              const float tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
-              const float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
-              const bool hit = (tnear <= tfar * 1.000001f);
-              const uint32_t code = __float_as_uint(hi.w);
-              if(hit && code != 0u) { first = code >> 3; count = code & 7u; }
-              node = (hit && code == 0u) ? node + 1u : __float_as_uint(lo.w);
-              if(node >= T.node_count) { node = BZ_END; }
-            }
-            if(count != 0u) {
-              const uint32_t at = atomicAdd(&P.qa_n, count);
-              for(uint32_t j = 0u; j < count; ++j) {
-                P.qa_leaf[at + j] = first + j;
-                P.qa_slot[at + j] = (uint8_t)slot;
-              }
-            }
-            room -= (uint32_t)__popc(__ballot_sync(0xffffffffu, count != 0u)) * BZ_LEAF_PUSH;
+            __syncwarp();
+            if(P.qa_n > BZ_QA_CAP - 32u * BZ_LEAF_PUSH * BZ_WALK_BURST) { break; }
           }
+          c_nodes += steps;
         }
         continue;
       }

@@ -244,9 +244,15 @@ void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out) {
       todo.push_back({ child, 0u, depth, 0 });
     }
     else {
-      uint32_t const link = static_cast<uint32_t>(out.nodes.size() / 8u);
+      uint32_t link = static_cast<uint32_t>(out.nodes.size() / 8u);      // patched to the end marker below if nothing follows
       std::memcpy(out.nodes.data() + job.flat * 8u + 3u, &link, sizeof(link));
       todo.pop_back();
     }
+  }
+  uint32_t const total = static_cast<uint32_t>(out.nodes.size() / 8u), endMarker = 0xffffffffu;
+  for(uint32_t i = 0u; i < total; ++i) {
+    uint32_t link;
+    std::memcpy(&link, out.nodes.data() + size_t(i) * 8u + 3u, sizeof(link));
+    if(link >= total) { std::memcpy(out.nodes.data() + size_t(i) * 8u + 3u, &endMarker, sizeof(endMarker)); }
   }
 }
