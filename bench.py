@@ -156,7 +156,7 @@ def main_ours(args, name):
     import torch
     import torch.distributed as dist
     import bezier_b200 as bz
-    from bezier_b200 import workloads
+    from bezier_b200 import sharding, workloads
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -195,7 +195,7 @@ def main_ours(args, name):
         flush.fill_(1)                                                                  # L2 flush between iterations
         lens.render_striped_device(cam, scene, stripe, rank, world, band, stats=stats)
         if world > 1:
-            dist.all_gather_into_tensor(bands, band)                                    # NCCL over NVLink
+            sharding.gather_bands(band, bands)                                          # NCCL all-gather over NVLink
             if rank == 0:
                 bz.assemble_stripes_device(bands, band_rows, width, height, stripe, world, image)
         if record:

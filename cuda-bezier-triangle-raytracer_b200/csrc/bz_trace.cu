@@ -36,7 +36,7 @@
 #endif
 #define BZ_SLOTS     (32 * BZ_GROUPS)
 #ifndef BZ_WALK_BURST
-#define BZ_WALK_BURST 4
+#define BZ_WALK_BURST 2
 #endif
 //        // hierarchy steps per lane between two looks at the level of queue A
 #ifndef BZ_QA_CAP
