@@ -1,0 +1,116 @@
+// bz_bezier_lens.h -- host C++ face of the refraction path: the reference's BezierLens (reference/bezierLens.h:7-28)
+// with the same names and argument meaning, implemented on top of the C ABI (include/bz_capi.h).  The lens owns the
+// device tables (SoA patch streams + cull hierarchy) of one CUDA device; every query runs in the sm_100a kernels.
+// There is no host arithmetic here and no CPU fallback: without a CUDA device the constructor throws.
+//
+// Single-ray methods keep API parity with the reference (they are batches of one); the batch methods are the real
+// entry points.  Header-only; link against libbz_b200.so.
+#ifndef BZ_BEZIER_LENS_H
+#define BZ_BEZIER_LENS_H
+
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+#include "bz_capi.h"
+#include "bz_bezier_mesh.h"
+#include "bz_geom.h"
+
+namespace bz {
+
+// reference/3dGeomUtil.h:168-206: the constructor normalises the direction
+struct Ray final {
+  Vertex mStart;
+  Vector mDirection;
+  Ray() = default;
+  Ray(Vertex const &aStart, Vector const &aDirection) : mStart(aStart), mDirection(normalized(aDirection)) {}
+};
+
+// reference/bezierLens.h:7-11
+enum class RefractionResult : uint32_t { cNone = BZ_STATUS_NONE, cInside = BZ_STATUS_INSIDE, cOutside = BZ_STATUS_OUTSIDE };
+
+// reference/bezierTriangle.h:7-20 (+ the index of the hit patch, which the reference does not report)
+struct BezierIntersection final {
+  enum class What : uint32_t { cFollowSide0 = 0u, cFollowSide1 = 1u, cFollowSide2 = 2u, cNone = BZ_WHAT_NONE, cIntersect = BZ_WHAT_INTERSECT };
+  bool     mValid;
+  Vertex   mPoint;
+  float    mCosIncidence;
+  float    mDistance;
+  Vertex   mBarycentric;
+  Vector   mNormal;
+  What     mWhat;
+  uint32_t mPatch;
+};
+
+class BezierLens final {
+public:
+  // BezierLens(float aRi, BezierMesh const&), reference/bezierLens.h:23
+  BezierLens(float const aRi, BezierMesh const &aMesh, int const aDevice = 0) : mRefractiveIndex(aRi), mPatchCount(static_cast<uint32_t>(aMesh.size())) {
+    check(bz_lens_create(aMesh.records(), mPatchCount, aRi, aDevice, &mLens));
+  }
+  ~BezierLens() { bz_lens_destroy(mLens); }
+  BezierLens(BezierLens &&aOther) noexcept : mRefractiveIndex(aOther.mRefractiveIndex), mPatchCount(aOther.mPatchCount), mLens(aOther.mLens) { aOther.mLens = nullptr; }
+  BezierLens(BezierLens const &) = delete;
+  BezierLens &operator=(BezierLens const &) = delete;
+
+  // std::pair<Ray, RefractionResult> refract(Ray const&, RefractionResult aExpected) const, reference/bezierLens.h:27.
+  // On cNone the returned ray is the incoming one (the reference leaves it partly uninitialised).
+  std::pair<Ray, RefractionResult> refract(Ray const &aRay, RefractionResult const aExpected) const {
+    float const start[3] = { aRay.mStart.x, aRay.mStart.y, aRay.mStart.z }, dir[3] = { aRay.mDirection.x, aRay.mDirection.y, aRay.mDirection.z };
+    uint32_t const expected = static_cast<uint32_t>(aExpected);
+    float outStart[3], outDir[3];
+    uint32_t status = 0u;
+    check(bz_refract_batch_host(mLens, start, dir, &expected, 1u, outStart, outDir, &status, nullptr));
+    Ray result;
+    result.mStart = Vec3{outStart[0], outStart[1], outStart[2]};
+    result.mDirection = Vec3{outDir[0], outDir[1], outDir[2]};
+    return std::make_pair(result, static_cast<RefractionResult>(status));
+  }
+
+  // the same over n host rays (3 floats each); results in caller-owned arrays, aOutPatch may be null
+  void refract(float const *aStart, float const *aDirection, uint32_t const *aExpected, uint64_t const aCount,
+               float *aOutStart, float *aOutDirection, uint32_t *aOutStatus, uint32_t *aOutPatch = nullptr) const {
+    check(bz_refract_batch_host(mLens, aStart, aDirection, aExpected, aCount, aOutStart, aOutDirection, aOutStatus, aOutPatch));
+  }
+
+  // BezierIntersection BezierMesh::intersect(Ray const&) const, reference/bezierMesh.h:37
+  BezierIntersection intersect(Ray const &aRay) const {
+    float const start[3] = { aRay.mStart.x, aRay.mStart.y, aRay.mStart.z }, dir[3] = { aRay.mDirection.x, aRay.mDirection.y, aRay.mDirection.z };
+    uint32_t what = 0u, patch = 0u;
+    float distance = 0.0f, cosine = 0.0f, point[3], normal[3], bary[3];
+    check(bz_intersect_batch_host(mLens, start, dir, 1u, &what, &patch, &distance, point, normal, &cosine, bary));
+    BezierIntersection result;
+    result.mWhat = static_cast<BezierIntersection::What>(what);
+    result.mValid = (what == BZ_WHAT_INTERSECT);
+    result.mPatch = patch;
+    result.mDistance = distance;
+    result.mCosIncidence = cosine;
+    result.mPoint = Vec3{point[0], point[1], point[2]};
+    result.mNormal = Vec3{normal[0], normal[1], normal[2]};
+    result.mBarycentric = Vec3{bary[0], bary[1], bary[2]};
+    return result;
+  }
+
+  // headless render of rows [aRow0, aRow1) into a host RGBA8 buffer (definitions in include/bz_capi.h)
+  void render(bz_camera const &aCamera, bz_scene const &aScene, uint32_t const aRow0, uint32_t const aRow1, uint8_t *aRgba, bz_stats *aStats = nullptr) const {
+    check(bz_render_host(mLens, &aCamera, &aScene, aRow0, aRow1, aRgba, aStats));
+  }
+
+  float getRefractiveIndex() const { return mRefractiveIndex; }
+  uint32_t size() const { return mPatchCount; }
+  bz_lens *handle() const { return mLens; }       // for the device-pointer entry points of the C ABI
+
+private:
+  float    mRefractiveIndex;
+  uint32_t mPatchCount;
+  bz_lens *mLens = nullptr;
+
+  static void check(int const aCode) {
+    if(aCode != BZ_OK) { throw std::runtime_error("libbz_b200 error " + std::to_string(aCode) + ": " + bz_last_error()); }
+  }
+};
+
+}
+
+#endif

@@ -1,0 +1,57 @@
+// Test program for the host C++ API (bz::Mesh -> bz::BezierMesh -> bz::BezierLens), compiled and run by
+// tests/test_cpp_api.py.  Usage: cpp_api_check [gpu].  Without a CUDA device the lens constructor must throw
+// (there is no CPU path); with "gpu" it refracts the SURVEY.md section 4 anchor ray through the unit sphere.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include "bz_bezier_lens.h"
+
+int main(int argc, char **argv) {
+  bool const gpu = (argc > 1 && std::strcmp(argv[1], "gpu") == 0);
+  bz::Mesh mesh;
+  mesh.makeUnitSphere(16, 8);
+  mesh.standardizeVertices();
+  mesh.standardizeNormals();
+  if(mesh.size() != 256u || mesh.getFace2neighbours().size() != 256u) { std::printf("bad mesh\n"); return 1; }
+  bz::BezierMesh bezier(mesh);
+  if(bezier.size() != 768u) { std::printf("bad bezier mesh\n"); return 1; }
+  auto const neighbours = bezier[0u].getNeighbours();               // patch 0 neighbours {91, 1, 2}
+  if(neighbours[0] != 91u || neighbours[1] != 1u || neighbours[2] != 2u) { std::printf("bad neighbours\n"); return 1; }
+  try {                                                              // skipping standardizeNormals: std::out_of_range
+    bz::Mesh raw;
+    raw.makeUnitSphere(8, 4);
+    bz::BezierMesh broken(raw);
+    std::printf("missing out_of_range\n");
+    return 1;
+  }
+  catch(std::out_of_range const &) {}
+  try {
+    bz::Mesh bad;
+    bad.makeEllipsoid(182, 91, bz::Vec3{1.0f, 4.0f, 2.0f});
+    bad.standardizeVertices();
+    bad.standardizeNormals();
+    std::printf("missing throw\n");
+    return 1;
+  }
+  catch(char const *text) { if(std::strcmp(text, "Vertex on edge detected.") != 0) { return 1; } }   // mesh.cpp:204
+  try {
+    bz::BezierLens lens(1.3f, bezier);
+    if(!gpu) { std::printf("lens built without a device?\n"); return 1; }
+    bz::Ray ray(bz::Vec3{-10.0f, 0.1f, 0.2f}, bz::Vec3{2.0f, 0.0f, 0.0f});
+    auto const hit = lens.intersect(ray);
+    if(hit.mWhat != bz::BezierIntersection::What::cIntersect || hit.mPatch != 350u) { std::printf("bad hit %u\n", hit.mPatch); return 1; }
+    auto const in = lens.refract(ray, bz::RefractionResult::cInside);
+    if(in.second != bz::RefractionResult::cInside) { std::printf("no entry\n"); return 1; }
+    auto const out = lens.refract(in.first, bz::RefractionResult::cOutside);
+    if(out.second != bz::RefractionResult::cOutside || std::fabs(out.first.mDirection.x - 0.99463236f) > 2e-6f) { std::printf("bad exit\n"); return 1; }
+    auto const wrong = lens.refract(ray, bz::RefractionResult::cOutside);
+    if(wrong.second != bz::RefractionResult::cNone) { std::printf("expected-side check failed\n"); return 1; }
+    std::printf("ok gpu\n");
+  }
+  catch(std::runtime_error const &e) {
+    if(gpu) { std::printf("lens failed: %s\n", e.what()); return 1; }
+    std::printf("ok cpu (%s)\n", e.what());
+  }
+  return 0;
+}

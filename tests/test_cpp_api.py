@@ -1,0 +1,30 @@
+"""The host C++ API (host/bz_mesh.h, bz_bezier_mesh.h, bz_bezier_lens.h) used the way a reference caller would."""
+import os
+import subprocess
+
+import pytest
+
+import common
+
+PKG = os.path.join(common.ROOT, "cuda-bezier-triangle-raytracer_b200")
+
+
+def build(tmp_path):
+    exe = str(tmp_path / "cpp_api_check")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(PKG, "host"), "-I" + os.path.join(common.ROOT, "include"),
+                           os.path.join(common.ROOT, "tests", "cpp_api_check.cpp"), "-L" + PKG, "-lbz_b200", "-Wl,-rpath," + PKG, "-o", exe])
+    return exe
+
+
+def test_cpp_api_without_device(tmp_path):
+    import bezier_b200 as bz
+    if bz.device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    out = subprocess.check_output([build(tmp_path)]).decode()
+    assert out.startswith("ok cpu") and "no usable CUDA device" in out
+
+
+@pytest.mark.gpu
+def test_cpp_api_on_device(tmp_path):
+    out = subprocess.check_output([build(tmp_path), "gpu"]).decode()
+    assert out.strip() == "ok gpu"
