@@ -85,3 +85,21 @@ def test_cuda_path_matches_golden(name, mode):
     assert np.array_equal(st1, g["r_status1"]) and common.same_bits(s1, g["r_start1"]) and common.same_bits(d1, g["r_dir1"])
     s2, d2, st2, _ = lens.refract(g["r_start1"], g["r_dir1"], g["r_expected1"])
     assert np.array_equal(st2, g["r_status2"]) and common.same_bits(s2, g["r_start2"]) and common.same_bits(d2, g["r_dir2"])
+
+
+def test_reference_as_written_is_broken_on_this_path(oracle_built):
+    """compiled exactly as written, the reference reads an uninitialised mPoint in the root search
+    (3dGeomUtil.h:284-290 vs bezierTriangle.cpp:158-159) and loses almost every ray; the hoisted build is the oracle."""
+    import bzref
+    if not bzref.available(as_written=True):
+        pytest.skip("libbzref_aswritten.so not built")
+    ys, zs = np.meshgrid(np.linspace(-1.2, 1.2, 80, dtype=np.float32), np.linspace(-1.2, 1.2, 60, dtype=np.float32))
+    s = np.stack([np.full(ys.size, -10.0, np.float32), ys.ravel(), zs.ravel()], axis=1)
+    d = np.tile(np.array([[1, 0, 0]], np.float32), (s.shape[0], 1))
+    entered = {}
+    for as_written in (False, True):
+        m = bzref.RefMesh(as_written=as_written).make_unit_sphere(16, 8).standardize_vertices().standardize_normals()
+        lens = bzref.RefLens(1.3, bzref.RefBezierMesh(m))
+        entered[as_written] = int((lens.refract(s, d, 1, threads=4)[2] == 1).sum())
+    assert entered[False] > 2000                      # ~53 % of the grid enters the sphere
+    assert entered[True] < entered[False] // 4        # as written: a small fraction (what the garbage happens to allow)

@@ -109,13 +109,14 @@ def test_render_bands_and_stripes_compose(bz, oracle_built):
     bottom, _ = lens.render(cam, scene, 33, 70)
     assert np.array_equal(np.concatenate([top, bottom]), full)
     ranks, stripe = 4, 8
+    reserve = max(bz.striped_rows(cam.height, stripe, r, ranks) for r in range(ranks))
+    bands = torch.zeros((ranks, reserve, cam.width, 4), dtype=torch.uint8, device="cuda")       # what the all-gather leaves on a rank
     image = np.zeros_like(full)
     for rank in range(ranks):
         rows = bz.striped_rows(cam.height, stripe, rank, ranks)
-        buf = torch.zeros((rows, cam.width, 4), dtype=torch.uint8, device="cuda")
-        lens.render_striped_device(cam, scene, stripe, rank, ranks, buf)
+        lens.render_striped_device(cam, scene, stripe, rank, ranks, bands[rank])
         torch.cuda.synchronize()
-        local = buf.cpu().numpy()
+        local = bands[rank].cpu().numpy()
         r = 0
         for first in range(rank * stripe, cam.height, ranks * stripe):
             k = min(stripe, cam.height - first)
@@ -123,6 +124,10 @@ def test_render_bands_and_stripes_compose(bz, oracle_built):
             r += k
         assert r == rows
     assert np.array_equal(image, full)
+    assembled = torch.zeros((cam.height, cam.width, 4), dtype=torch.uint8, device="cuda")
+    bz.assemble_stripes_device(bands, reserve, cam.width, cam.height, stripe, ranks, assembled)  # bz_assemble_stripes
+    torch.cuda.synchronize()
+    assert np.array_equal(assembled.cpu().numpy(), full)
 
 
 def test_generate_rays_bit_exact(bz, oracle_built):
