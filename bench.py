@@ -186,7 +186,7 @@ def main_ours(args, name):
     band = torch.zeros((band_rows, width, 4), dtype=torch.uint8, device=dev)          # this rank's stripes (padded to the largest band)
     bands = torch.zeros((world, band_rows, width, 4), dtype=torch.uint8, device=dev) if world > 1 else None
     image = torch.zeros((height, width, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else None
-    stats = torch.zeros(9, dtype=torch.int64, device=dev)
+    stats = torch.zeros(len(bz.STAT_NAMES), dtype=torch.int64, device=dev)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)               # > 126 MB L2
     host_image = torch.empty((height, width, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
     kernel_ms = []

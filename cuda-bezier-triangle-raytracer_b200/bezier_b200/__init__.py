@@ -42,7 +42,8 @@ class Scene(C.Structure):
                 ("value_lost", C.c_uint32), ("max_crossings", C.c_uint32)]
 
 
-STAT_NAMES = ("primary_rays", "refract_calls", "stage_a", "stage_b", "snell", "entered", "exited", "lost", "node_visits")
+STAT_NAMES = ("primary_rays", "refract_calls", "stage_a", "stage_b", "snell", "entered", "exited", "lost", "node_visits",
+              "packet_nodes", "packet_walks", "lane_walk_calls")
 
 
 class Stats(C.Structure):

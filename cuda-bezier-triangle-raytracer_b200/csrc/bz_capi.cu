@@ -39,7 +39,7 @@ struct bz_lens {
   int        sm_count;
   uint32_t   mode;
   bz_tables  tables;
-  float4    *d_cull, *d_newton, *d_leaf, *d_nodes;
+  float4    *d_cull, *d_newton, *d_leaf, *d_nodes, *d_packet;
   unsigned long long *d_counter;      // work counter of the persistent kernel
   uint32_t  *d_accum;                 // render scratch: one u32 per pixel of the largest band so far
   size_t     accum_pixels;
@@ -83,7 +83,7 @@ uint32_t bz_sizeof_stats(void) { return (uint32_t)sizeof(bz_stats); }
 int bz_lens_destroy(bz_lens *lens) {
   if(lens == nullptr) { return BZ_OK; }
   cudaSetDevice(lens->device);
-  cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_nodes);
+  cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_nodes); cudaFree(lens->d_packet);
   cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch);
   if(lens->ev_begin) { cudaEventDestroy(lens->ev_begin); }
   if(lens->ev_end) { cudaEventDestroy(lens->ev_end); }
@@ -151,6 +151,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   if(e == cudaSuccess) { e = upload(newton, &lens->d_newton); }
   if(e == cudaSuccess) { e = upload(leaf, &lens->d_leaf); }
   if(e == cudaSuccess) { e = upload(bvh.nodes, &lens->d_nodes); }
+  if(e == cudaSuccess) { e = upload(bvh.packet_nodes, &lens->d_packet); }
   if(e == cudaSuccess) { e = cudaMalloc((void**)&lens->d_counter, 64u); }
   if(e == cudaSuccess) { e = cudaEventCreate(&lens->ev_begin); }
   if(e == cudaSuccess) { e = cudaEventCreate(&lens->ev_end); }
@@ -163,6 +164,8 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   lens->tables.newton = lens->d_newton;
   lens->tables.leaf = lens->d_leaf;
   lens->tables.nodes = lens->d_nodes;
+  lens->tables.packet = (const float*)lens->d_packet;
+  lens->tables.packet_count = (uint32_t)(bvh.packet_nodes.size() / 224u);
   lens->tables.patch_count = patch_count;
   lens->tables.node_count = (uint32_t)(bvh.nodes.size() / 8u);
   lens->tables.wide_first = (uint32_t)bvh.order.size();

@@ -8,6 +8,9 @@
 //   leaf     4 float4 per leaf slot: the cull records again, in BVH leaf order, followed by the "wide"
 //            segment (tested directly only by rays starting beyond origin_limit) and the "always"
 //            segment (patches the cull cannot bound, tested for every ray)
+//   packet   7 x 32 words per node of the same hierarchy collapsed to 32 children per node (one lane per child):
+//            lo.x[32] lo.y[32] lo.z[32] hi.x[32] hi.y[32] hi.z[32] code[32]; code 0 = empty child, bit 31 = inner child
+//            (low bits: node index), else first_slot << 3 | count
 //   nodes    2 float4 per node of the binary cull hierarchy, depth-first order:
 //            [0] box lo.xyz, skip link (index of the first node after this subtree, taken when the box is missed)
 //            [1] box hi.xyz, leaf code (0: inner node, its first child is the next node; else first_slot << 3 | count)
@@ -28,6 +31,8 @@ struct bz_tables {
   const float4 *newton;
   const float4 *leaf;
   const float4 *nodes;
+  const float  *packet;    // the hierarchy again, 32 children per node, 7 x 32 words per node (host/bz_bvh.h)
+  uint32_t packet_count;
   uint32_t patch_count;
   uint32_t node_count;
   uint32_t wide_first;     // slots [wide_first, always_first): copies of the ill-conditioned patches whose grown boxes are

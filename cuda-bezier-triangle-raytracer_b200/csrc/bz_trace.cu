@@ -8,12 +8,18 @@
 // Every WARP is its own scheduler: it owns a pool of BZ_SLOTS = 32 * BZ_GROUPS ray slots and two work queues in
 // shared memory and never meets another warp at a barrier.  One pass of its loop is one refract() call for every live
 // slot:
-//   refill     dead slots take the next primary-ray indices from a global counter (one atomic per warp and group);
-//              live rays stay where they are, so the pool stays compacted across bounces
-//   walk       per lane, the cull hierarchy in depth-first order with skip links (no stack): boxes of the flat
-//              underlying triangles, conservative slab test; leaf hits push (slot, leaf record) pairs to queue A
-//   stage A    queue A is consumed 32 pairs at a time: plane hit, self-hit gate, barycentric inside test
-//              (bezierTriangle.cpp:124-131); survivors go to queue B
+//   refill     a group whose 32 rays are all finished takes the next 32 primary-ray indices from a global counter (one
+//              atomic per warp and group): consecutive rays are neighbours on the image, and the rays of a group stay
+//              together across bounces, so a group is a coherent packet
+//   walk       PACKET walk first: the 32 rays of a group are bounded by an origin box and a direction box (CREDUX.F32
+//              warp reductions), and the warp walks the 32-children-per-node form of the cull hierarchy cooperatively,
+//              ONE LANE PER CHILD BOX, with a conservative interval slab test and a node stack in shared memory; the
+//              leaves the packet may meet become a candidate list.  A packet that is not coherent enough (candidate
+//              list or stack overflow) falls back to the LANE walk: per lane, the binary hierarchy in depth-first
+//              order with skip links (no stack), leaf hits push (slot, leaf record) pairs to queue A
+//   stage A    plane hit, self-hit gate, barycentric inside test (bezierTriangle.cpp:124-131); survivors go to queue B.
+//              Packet candidates are tested record by record by all rays of the group at once (one broadcast record
+//              load per patch); queue A pairs of the lane walk are consumed 32 at a time
 //   stage B    queue B is consumed 32 candidates at a time, whatever slot they belong to: bracket + 4 root-search steps
 //              (cpp:132-194); follow-side results are appended to queue B as one-hop candidates (bezierMesh.cpp:213-217);
 //              the nearest hit per slot is a 64-bit shared-memory atomicMin on (distance, loop index) -- the reference's
@@ -28,7 +34,7 @@
 #include "bz_math.cuh"
 
 #ifndef BZ_GROUPS
-#define BZ_GROUPS    1
+#define BZ_GROUPS    2
 #endif
 #define BZ_WARPS     4
 #ifndef BZ_MIN_CTAS
@@ -40,12 +46,16 @@
 #endif
 //        // hierarchy steps per lane between two looks at the level of queue A
 #ifndef BZ_QA_CAP
-#define BZ_QA_CAP    512
+#define BZ_QA_CAP    256
 #endif
+#ifndef BZ_CAND_CAP
+#define BZ_CAND_CAP  96      // leaves a packet may collect before it is declared incoherent
+#endif
+#define BZ_STACK_CAP 96
 #define BZ_QB_CAP    160
 #define BZ_LEAF_PUSH BZ_LEAF_MAX // upper bound of pairs one lane pushes in one walk step
 #define BZ_KEY_NONE  0xffffffffffffffffull
-#define BZ_NSTAT     9
+#define BZ_NSTAT     12
 #define BZ_END       0xffffffffu
 
 struct bz_warp_pool {
@@ -60,6 +70,8 @@ struct bz_warp_pool {
   uint32_t           qb_loop[BZ_QB_CAP];     //          loop index of the candidate (the originating patch for a hop)
   uint8_t            qa_slot[BZ_QA_CAP];
   uint8_t            qb_slot[BZ_QB_CAP];     //          slot | 0x80 for a first-level candidate (inside test applies, may hop)
+  uint32_t           cand[BZ_CAND_CAP];      // packet walk: leaf codes (first slot << 3 | count) the packet may meet
+  uint32_t           stack[BZ_STACK_CAP];    // packet walk: 32-wide nodes still to visit
   uint32_t           qa_n, qb_n;
 };
 
@@ -137,6 +149,40 @@ __device__ __forceinline__ float bzw_key_distance(unsigned long long key) {
   return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 
+// CREDUX.{MIN,MAX}.F32: warp-wide float reduction into a uniform register, one instruction (sm_100a)
+__device__ __forceinline__ float bzw_warp_min(float v) { float r; asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v)); return r; }
+__device__ __forceinline__ float bzw_warp_max(float v) { float r; asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v)); return r; }
+
+// One axis of the packet's interval slab test.  Every ray of the packet has origin o in [o_lo, o_hi] and direction d in
+// [d_lo, d_hi] on this axis, so for t >= 0 its coordinate lies in [o_lo + t d_lo, o_hi + t d_hi]; it can be inside the
+// slab [lo - m, hi + m] only if   o_lo + t d_lo <= hi + m   and   o_hi + t d_hi >= lo - m.   Each is one bound on t whose
+// kind (upper / lower) follows from the sign of d_lo resp. d_hi, the same for all boxes.
+struct bzw_axis {
+  float inv1, c1, inv2, c2;     // t1 = hi * inv1 + c1,  t2 = lo * inv2 + c2
+  bool  upper1, lower2;         // t1 is an upper bound (d_lo > 0), else a lower one; t2 is a lower bound (d_hi > 0), else an upper one
+};
+
+__device__ __forceinline__ bzw_axis bzw_make_axis(float o_lo, float o_hi, float d_lo, float d_hi, float margin) {
+  bzw_axis a;
+  // a vanishing slope is pushed to the permissive side (the lane walk treats |d| < 1e-20 the same way)
+  if(fabsf(d_lo) < 1e-20f) { d_lo = -1e-20f; }
+  if(fabsf(d_hi) < 1e-20f) { d_hi = 1e-20f; }
+  a.inv1 = 1.0f / d_lo;
+  a.inv2 = 1.0f / d_hi;
+  a.c1 = (margin - o_lo) * a.inv1;
+  a.c2 = (-margin - o_hi) * a.inv2;
+  a.upper1 = d_lo > 0.0f;
+  a.lower2 = d_hi > 0.0f;
+  return a;
+}
+
+__device__ __forceinline__ void bzw_axis_bounds(const bzw_axis &a, float lo, float hi, float &tnear, float &tfar) {
+  const float inf = __int_as_float(0x7f800000);
+  const float t1 = __fmaf_rn(hi, a.inv1, a.c1), t2 = __fmaf_rn(lo, a.inv2, a.c2);
+  tnear = fmaxf(tnear, fmaxf(a.upper1 ? -inf : t1, a.lower2 ? t2 : -inf));
+  tfar = fminf(tfar, fminf(a.upper1 ? t1 : inf, a.lower2 ? inf : t2));
+}
+
 template<int JOB>
 __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kernel(const bz_tables T, const bz_job J) {
   __shared__ bz_warp_pool pools[BZ_WARPS];
@@ -146,6 +192,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
   const uint32_t direct_end = T.always_first + T.always_count;
   unsigned long long c_primary = 0ull, c_calls = 0ull, c_a = 0ull, c_nodes = 0ull;
   uint32_t c_b = 0u, c_snell = 0u, c_enter = 0u, c_exit = 0u, c_lost = 0u;
+  uint32_t c_pnodes = 0u, c_pwalks = 0u, c_lwalks = 0u;     // lane 0 only: 32-wide nodes visited, packet walks, lane-walk fallbacks
   bool exhausted = false;                    // warp-uniform: the global ray counter has run past the end
 
 #pragma unroll
@@ -158,15 +205,17 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
     int group = 0;                           // warp-uniform: group whose walk is in progress; BZ_GROUPS = all walked
     bool group_ready = false;                // warp-uniform: refill of `group` done, walk state valid
     bool any_live = false;                   // warp-uniform
-    uint32_t node = BZ_END, direct = BZ_END; // per lane: walk state of the current group
+    uint32_t node = BZ_END, direct = BZ_END; // per lane: lane-walk state of the current group
+    uint32_t cand_n = 0u, cand_at = 0u, cand_sub = 0u, cand_group = 0u;   // warp-uniform: packet candidates still to be tested by stage A
 
     for(;;) {
       __syncwarp();
       const uint32_t qa = P.qa_n, qb = P.qb_n;
       __syncwarp();
       const bool walked = (group == BZ_GROUPS);
-      int action;                            // warp-uniform: 0 walk, 1 stage A batch, 2 stage B batch, 3 pass complete
+      int action;                            // warp-uniform: 0 walk, 1 stage A batch, 2 stage B batch, 3 pass complete, 4 stage A on packet candidates
       if(qb > BZ_QB_CAP - 64u) { action = 2; }
+      else if(cand_at < cand_n) { action = 4; }
       else if(qa > BZ_QA_CAP - 32u * BZ_LEAF_PUSH * BZ_WALK_BURST || (walked && qa != 0u)) { action = 1; }
       else if(!walked) { action = 0; }
       else if(qb != 0u) { action = 2; }
@@ -176,10 +225,15 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
       if(action == 0) {
         const uint32_t slot = (uint32_t)group * 32u + lane;
         if(!group_ready) {
-          // ---- refill: dead slots of this group take the next primary rays ----
+          // ---- refill: a group whose rays are all finished takes the next 32 primary rays ----
           uint32_t st = P.state[slot];
           bool live = (st & 1u) != 0u;
-          const uint32_t need = __ballot_sync(0xffffffffu, !live);
+          const uint32_t dead = __ballot_sync(0xffffffffu, !live);
+#ifdef BZ_REFILL_PARTIAL
+          const uint32_t need = dead;
+#else
+          const uint32_t need = (dead == 0xffffffffu) ? dead : 0u;
+#endif
           if(need != 0u && !exhausted) {
             unsigned long long base = 0ull;
             const int leader = __ffs(need) - 1;
@@ -218,13 +272,76 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             }
           }
           P.best[slot] = BZ_KEY_NONE;
-          any_live = any_live || (__ballot_sync(0xffffffffu, live) != 0u);
+          const uint32_t live_mask = __ballot_sync(0xffffffffu, live);
+          any_live = any_live || (live_mask != 0u);
+          if(live_mask == 0u) { ++group; continue; }      // nothing to walk in this group
+          const float sx = P.ray[0][slot], sy = P.ray[1][slot], sz = P.ray[2][slot];
+          const float l1 = fabsf(sx) + fabsf(sy) + fabsf(sz);
+          if(live) { ++c_calls; }
+          // ---- packet walk: one lane per child box of the 32-wide hierarchy ----
+          bool packet_done = false;
+          if(T.packet_count != 0u) {
+            const float inf = __int_as_float(0x7f800000);
+            const float dx = P.ray[3][slot], dy = P.ray[4][slot], dz = P.ray[5][slot];
+            const float l1_max = bzw_warp_max(live ? l1 : 0.0f);
+            // twice the largest per-ray slack of the lane walk: one share is the cull's own guarantee (host/bz_bvh.cpp),
+            // the other covers the rounding of the interval arithmetic below (a few ulp of |box| + |origin|)
+            const float margin = 2.0f * 3.0517578125e-05f * (l1_max + 2.0f * T.extent);
+            const bzw_axis ax = bzw_make_axis(bzw_warp_min(live ? sx : inf), bzw_warp_max(live ? sx : -inf),
+                                              bzw_warp_min(live ? dx : inf), bzw_warp_max(live ? dx : -inf), margin);
+            const bzw_axis ay = bzw_make_axis(bzw_warp_min(live ? sy : inf), bzw_warp_max(live ? sy : -inf),
+                                              bzw_warp_min(live ? dy : inf), bzw_warp_max(live ? dy : -inf), margin);
+            const bzw_axis az = bzw_make_axis(bzw_warp_min(live ? sz : inf), bzw_warp_max(live ? sz : -inf),
+                                              bzw_warp_min(live ? dz : inf), bzw_warp_max(live ? dz : -inf), margin);
+            const uint32_t below = (1u << lane) - 1u;
+            // records outside the hierarchy: the always segment, and the wide segment when a ray starts beyond origin_limit
+            const uint32_t direct_first = (l1_max <= T.origin_limit) ? T.always_first : T.wide_first;
+            const uint32_t direct_n = direct_end - direct_first;
+            uint32_t sp = 1u, found = (direct_n + 6u) / 7u;
+            packet_done = (found <= BZ_CAND_CAP / 2u);
+            if(packet_done) {
+              if(lane < found) { P.cand[lane] = ((direct_first + 7u * lane) << 3) | min(7u, direct_n - 7u * lane); }
+              if(lane == 0u) { P.stack[0] = 0u; }
+              __syncwarp();
+            }
+            uint32_t visits = 0u;
+            while(packet_done && sp != 0u) {
+              --sp;
+              const float *box = T.packet + (size_t)P.stack[sp] * 224u + lane;
+              const float lox = __ldg(box), loy = __ldg(box + 32), loz = __ldg(box + 64);
+              const float hix = __ldg(box + 96), hiy = __ldg(box + 128), hiz = __ldg(box + 160);
+              const uint32_t code = __float_as_uint(__ldg(box + 192));
+              float tnear = 0.0f, tfar = inf;
+              bzw_axis_bounds(ax, lox, hix, tnear, tfar);
+              bzw_axis_bounds(ay, loy, hiy, tnear, tfar);
+              bzw_axis_bounds(az, loz, hiz, tnear, tfar);
+              const bool hit = (code != 0u) && (tnear <= tfar);
+              const bool inner = (code & 0x80000000u) != 0u;
+              const uint32_t hit_inner = __ballot_sync(0xffffffffu, hit && inner);
+              const uint32_t hit_leaf = __ballot_sync(0xffffffffu, hit && !inner);
+              ++visits;
+              if(sp + __popc(hit_inner) > BZ_STACK_CAP || found + __popc(hit_leaf) > BZ_CAND_CAP) { packet_done = false; break; }
+              if(hit && inner) { P.stack[sp + __popc(hit_inner & below)] = code & 0x7fffffffu; }
+              if(hit && !inner) { P.cand[found + __popc(hit_leaf & below)] = code; }
+              sp += __popc(hit_inner);
+              found += __popc(hit_leaf);
+              __syncwarp();
+            }
+            if(lane == 0u) { c_pnodes += visits; }
+            if(packet_done) {
+              cand_n = found; cand_at = 0u; cand_sub = 0u; cand_group = (uint32_t)group;
+              if(lane == 0u) { ++c_pwalks; }
+              ++group;
+              continue;
+            }
+            __syncwarp();
+          }
+          // ---- lane walk (no packet hierarchy, or the packet was not coherent enough) ----
           if(live) {
-            const float l1 = fabsf(P.ray[0][slot]) + fabsf(P.ray[1][slot]) + fabsf(P.ray[2][slot]);
             direct = (l1 <= T.origin_limit) ? T.always_first : T.wide_first;     // far origins also test the wide segment
             if(direct >= direct_end) { direct = BZ_END; }
             node = (T.node_count != 0u) ? 0u : BZ_END;
-            ++c_calls;
+            ++c_lwalks;
           }
           else {
             direct = BZ_END;
@@ -297,6 +414,36 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           }
           c_nodes += steps;
         }
+        continue;
+      }
+
+      if(action == 4) {
+        // ---- stage A, packet form: every candidate record is tested by all live rays of its group at once ----
+        const uint32_t slot = cand_group * 32u + lane;
+        const bool live = (P.state[slot] & 1u) != 0u;
+        const bzv3 s = bz_v(P.ray[0][slot], P.ray[1][slot], P.ray[2][slot]);
+        const bzv3 d = bz_v(P.ray[3][slot], P.ray[4][slot], P.ray[5][slot]);
+        const uint32_t below = (1u << lane) - 1u;
+        uint32_t level = qb;                  // warp-uniform copy of the level of queue B
+        while(cand_at < cand_n && level <= BZ_QB_CAP - 64u) {
+          const uint32_t code = P.cand[cand_at];
+          bz_cull_rec c;
+          uint32_t patch;
+          bzw_unpack_cull(T.leaf + (size_t)((code >> 3) + cand_sub) * BZ_CULL_F4, c, patch);     // one address for the warp: a broadcast load
+          float cosine, distance;
+          const bool pass = live && bz_stage_a(c, s, d, true, cosine, distance);
+          const uint32_t passed = __ballot_sync(0xffffffffu, pass);
+          if(pass) {
+            const uint32_t at = level + __popc(passed & below);
+            P.qb_patch[at] = patch;
+            P.qb_loop[at] = patch;
+            P.qb_slot[at] = (uint8_t)(slot | 0x80u);
+          }
+          level += __popc(passed);
+          if(live) { ++c_a; }
+          if(++cand_sub == (code & 7u)) { cand_sub = 0u; ++cand_at; }
+        }
+        if(lane == 0u) { P.qb_n = level; }
         continue;
       }
 
@@ -471,7 +618,8 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
   // ---- work counters: warp reduce, one atomic per warp and counter ----
   if(J.stats != nullptr) {
     unsigned long long v[BZ_NSTAT] = { c_primary, c_calls, c_a, (unsigned long long)c_b, (unsigned long long)c_snell,
-                                       (unsigned long long)c_enter, (unsigned long long)c_exit, (unsigned long long)c_lost, c_nodes };
+                                       (unsigned long long)c_enter, (unsigned long long)c_exit, (unsigned long long)c_lost, c_nodes,
+                                       (unsigned long long)c_pnodes, (unsigned long long)c_pwalks, (unsigned long long)c_lwalks };
 #pragma unroll
     for(int i = 0; i < BZ_NSTAT; ++i) {
       unsigned long long x = v[i];

@@ -146,6 +146,8 @@ void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out) {
   out.depth = 0u;
   out.wide.clear();
   out.origin_limit = 0.0f;
+  out.packet_nodes.clear();
+  out.packet_depth = 0u;
   Builder b;
   std::vector<uint32_t> prims;     // primitive -> patch
   std::vector<double> kappas(count, std::numeric_limits<double>::infinity());
@@ -247,6 +249,53 @@ void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out) {
       uint32_t link = static_cast<uint32_t>(out.nodes.size() / 8u);      // patched to the end marker below if nothing follows
       std::memcpy(out.nodes.data() + job.flat * 8u + 3u, &link, sizeof(link));
       todo.pop_back();
+    }
+  }
+  // the same tree collapsed to 32 children per node: a node's child set starts as its two binary children and the
+  // inner member with the largest box is replaced by its own two children until 32 are reached or only leaves remain
+  {
+    struct Wide { int binary; uint32_t depth; };
+    std::vector<Wide> queue;
+    queue.push_back({ root, 1u });
+    for(size_t at = 0u; at < queue.size(); ++at) {
+      Wide const job = queue[at];
+      out.packet_depth = std::max(out.packet_depth, job.depth);
+      std::vector<int> members;
+      if(b.nodes[job.binary].left < 0) { members.push_back(job.binary); }
+      else { members.push_back(b.nodes[job.binary].left); members.push_back(b.nodes[job.binary].right); }
+      while(members.size() < 32u) {
+        int pick = -1;
+        double area = -1.0;
+        for(size_t m = 0u; m < members.size(); ++m) {
+          Binary const &cand = b.nodes[members[m]];
+          if(cand.left >= 0 && cand.box.area() > area) { area = cand.box.area(); pick = static_cast<int>(m); }
+        }
+        if(pick < 0) { break; }
+        Binary const &open = b.nodes[members[pick]];
+        members[pick] = open.left;
+        members.push_back(open.right);
+      }
+      size_t const base = at * 224u;
+      if(out.packet_nodes.size() < base + 224u) { out.packet_nodes.resize(base + 224u, 0.0f); }
+      for(uint32_t lane = 0u; lane < 32u; ++lane) {
+        float *p = out.packet_nodes.data() + base;
+        uint32_t code = 0u;
+        if(lane < members.size()) {
+          Binary const &child = b.nodes[members[lane]];
+          for(int k = 0; k < 3; ++k) { p[32 * k + lane] = child.box.lo[k]; p[32 * (3 + k) + lane] = child.box.hi[k]; }
+          if(child.left < 0) { code = (child.first << 3u) | child.count; }
+          else {
+            code = 0x80000000u | static_cast<uint32_t>(queue.size());
+            queue.push_back({ members[lane], job.depth + 1u });
+            out.packet_nodes.resize(queue.size() * 224u, 0.0f);
+            p = out.packet_nodes.data() + base;
+          }
+        }
+        else {
+          for(int k = 0; k < 3; ++k) { p[32 * k + lane] = 3.0e38f; p[32 * (3 + k) + lane] = -3.0e38f; }
+        }
+        std::memcpy(p + 192 + lane, &code, sizeof(code));
+      }
     }
   }
   uint32_t const total = static_cast<uint32_t>(out.nodes.size() / 8u), endMarker = 0xffffffffu;

@@ -15,6 +15,11 @@ struct bz_bvh {
   float                 extent;   // max |coordinate| of the flat triangles
   float                 origin_limit;
   uint32_t              depth;    // levels of the binary hierarchy
+  // the same hierarchy collapsed to 32 children per node, for the warp-cooperative packet walk (one lane per child):
+  // 7 x 32 words per node: lo.x[32] lo.y[32] lo.z[32] hi.x[32] hi.y[32] hi.z[32] code[32]
+  // code: 0 = empty child, bit 31 set = inner child (low bits: packet node index), else first_slot << 3 | count
+  std::vector<float>    packet_nodes;
+  uint32_t              packet_depth;
 };
 
 void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out);

@@ -96,7 +96,10 @@ typedef struct bz_stats {
   uint64_t entered;          /* refract() returned cInside */
   uint64_t exited;           /* refract() returned cOutside */
   uint64_t lost;             /* primary rays shaded value_lost */
-  uint64_t node_visits;      /* 4-wide cull-hierarchy nodes visited (0 in BZ_MODE_BRUTE) */
+  uint64_t node_visits;      /* binary cull-hierarchy nodes visited by the per-lane walk (0 in BZ_MODE_BRUTE) */
+  uint64_t packet_nodes;     /* 32-children nodes visited by the warp-cooperative packet walk */
+  uint64_t packet_walks;     /* packet walks that completed (one per group of <= 32 rays and refract() call) */
+  uint64_t lane_walk_calls;  /* refract() calls whose packet was not coherent enough and walked per lane */
 } bz_stats;
 
 typedef struct bz_lens bz_lens;

@@ -32,7 +32,8 @@ class Scene(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in
-                ("primary_rays", "refract_calls", "stage_a", "stage_b", "snell", "entered", "exited", "lost", "node_visits")]
+                ("primary_rays", "refract_calls", "stage_a", "stage_b", "snell", "entered", "exited", "lost", "node_visits",
+                 "packet_nodes", "packet_walks", "lane_walk_calls")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
