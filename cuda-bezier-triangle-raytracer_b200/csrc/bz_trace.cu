@@ -34,11 +34,11 @@
 #include "bz_math.cuh"
 
 #ifndef BZ_GROUPS
-#define BZ_GROUPS    2
+#define BZ_GROUPS    1
 #endif
 #define BZ_WARPS     4
 #ifndef BZ_MIN_CTAS
-#define BZ_MIN_CTAS  5
+#define BZ_MIN_CTAS  4
 #endif
 #define BZ_SLOTS     (32 * BZ_GROUPS)
 #ifndef BZ_WALK_BURST
@@ -73,7 +73,13 @@ struct bz_warp_pool {
   uint32_t           cand[BZ_CAND_CAP];      // packet walk: leaf codes (first slot << 3 | count) the packet may meet
   uint32_t           stack[BZ_STACK_CAP];    // packet walk: 32-wide nodes still to visit
   uint32_t           qa_n, qb_n;
+  unsigned long long count[BZ_NSTAT];        // work counters of this warp (bz_stats order), kept out of the register file
 };
+
+// work counters live in shared memory and are bumped by lane 0 with warp-level totals
+// (the amount is evaluated by every lane: it may contain a warp vote)
+#define BZW_COUNT(index, amount) do { const unsigned long long amount_ = (unsigned long long)(amount); if(lane == 0u) { P.count[index] += amount_; } } while(0)
+enum { BZC_PRIMARY = 0, BZC_CALLS, BZC_STAGE_A, BZC_STAGE_B, BZC_SNELL, BZC_ENTER, BZC_EXIT, BZC_LOST, BZC_NODES, BZC_PNODES, BZC_PWALKS, BZC_LWALKS };
 
 static_assert(BZ_SLOTS <= 128, "queue entries keep the slot in 7 bits");
 static_assert(BZ_QA_CAP >= 32 * BZ_LEAF_PUSH * BZ_WALK_BURST + 64 && BZ_QB_CAP >= 96, "queue thresholds");
@@ -135,8 +141,15 @@ __device__ __forceinline__ uint32_t bzw_shade_background(const bz_scene &sc, con
   bzv3 p = bz_v(start.x + distance * dir.x, start.y + distance * dir.y, start.z + distance * dir.z);
   float ca = floorf(bz_dot(p, bz_v(sc.bg_axis_a[0], sc.bg_axis_a[1], sc.bg_axis_a[2])) / sc.cell);
   float cb = floorf(bz_dot(p, bz_v(sc.bg_axis_b[0], sc.bg_axis_b[1], sc.bg_axis_b[2])) / sc.cell);
+#ifdef BZ_CHECKER_FMOD
   float pa = fabsf(fmodf(ca, 2.0f));
   float pb = fabsf(fmodf(cb, 2.0f));
+#else
+  // |fmodf(c, 2)| for an integral-valued c, computed exactly without the library routine: c/2, floor, the doubling and
+  // the difference are all exact in FP32 (and an infinite or NaN c gives NaN either way)
+  float pa = fabsf(ca - 2.0f * floorf(ca * 0.5f));
+  float pb = fabsf(cb - 2.0f * floorf(cb * 0.5f));
+#endif
   return (pa != pb) ? sc.value_bright : sc.value_dark;
 }
 
@@ -190,14 +203,12 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t spp = J.camera.strata * J.camera.strata;
   const uint32_t direct_end = T.always_first + T.always_count;
-  unsigned long long c_primary = 0ull, c_calls = 0ull, c_a = 0ull, c_nodes = 0ull;
-  uint32_t c_b = 0u, c_snell = 0u, c_enter = 0u, c_exit = 0u, c_lost = 0u;
-  uint32_t c_pnodes = 0u, c_pwalks = 0u, c_lwalks = 0u;     // lane 0 only: 32-wide nodes visited, packet walks, lane-walk fallbacks
   bool exhausted = false;                    // warp-uniform: the global ray counter has run past the end
 
 #pragma unroll
   for(int g = 0; g < BZ_GROUPS; ++g) { P.state[g * 32 + lane] = 0u; }
   if(lane == 0u) { P.qa_n = 0u; P.qb_n = 0u; }
+  if(lane < BZ_NSTAT) { P.count[lane] = 0ull; }
   __syncwarp();
 
   for(;;) {
@@ -267,17 +278,17 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
                 st = 1u | (expected << 1);
                 P.state[slot] = st;
                 live = true;
-                ++c_primary;
               }
             }
           }
           P.best[slot] = BZ_KEY_NONE;
           const uint32_t live_mask = __ballot_sync(0xffffffffu, live);
           any_live = any_live || (live_mask != 0u);
+          BZW_COUNT(BZC_PRIMARY, __popc(live_mask & need));
+          BZW_COUNT(BZC_CALLS, __popc(live_mask));
           if(live_mask == 0u) { ++group; continue; }      // nothing to walk in this group
           const float sx = P.ray[0][slot], sy = P.ray[1][slot], sz = P.ray[2][slot];
           const float l1 = fabsf(sx) + fabsf(sy) + fabsf(sz);
-          if(live) { ++c_calls; }
           // ---- packet walk: one lane per child box of the 32-wide hierarchy ----
           bool packet_done = false;
           if(T.packet_count != 0u) {
@@ -327,21 +338,21 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
               found += __popc(hit_leaf);
               __syncwarp();
             }
-            if(lane == 0u) { c_pnodes += visits; }
+            BZW_COUNT(BZC_PNODES, visits);
             if(packet_done) {
               cand_n = found; cand_at = 0u; cand_sub = 0u; cand_group = (uint32_t)group;
-              if(lane == 0u) { ++c_pwalks; }
+              BZW_COUNT(BZC_PWALKS, 1u);
               ++group;
               continue;
             }
             __syncwarp();
           }
           // ---- lane walk (no packet hierarchy, or the packet was not coherent enough) ----
+          BZW_COUNT(BZC_LWALKS, __popc(live_mask));
           if(live) {
             direct = (l1 <= T.origin_limit) ? T.always_first : T.wide_first;     // far origins also test the wide segment
             if(direct >= direct_end) { direct = BZ_END; }
             node = (T.node_count != 0u) ? 0u : BZ_END;
-            ++c_lwalks;
           }
           else {
             direct = BZ_END;
@@ -412,7 +423,8 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             __syncwarp();
             if(P.qa_n > BZ_QA_CAP - 32u * BZ_LEAF_PUSH * BZ_WALK_BURST) { break; }
           }
-          c_nodes += steps;
+          steps = __reduce_add_sync(0xffffffffu, steps);
+          BZW_COUNT(BZC_NODES, steps);
         }
         continue;
       }
@@ -425,6 +437,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
         const bzv3 d = bz_v(P.ray[3][slot], P.ray[4][slot], P.ray[5][slot]);
         const uint32_t below = (1u << lane) - 1u;
         uint32_t level = qb;                  // warp-uniform copy of the level of queue B
+        uint32_t tested = 0u;
         while(cand_at < cand_n && level <= BZ_QB_CAP - 64u) {
           const uint32_t code = P.cand[cand_at];
           bz_cull_rec c;
@@ -440,10 +453,11 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             P.qb_slot[at] = (uint8_t)(slot | 0x80u);
           }
           level += __popc(passed);
-          if(live) { ++c_a; }
+          ++tested;
           if(++cand_sub == (code & 7u)) { cand_sub = 0u; ++cand_at; }
         }
         if(lane == 0u) { P.qb_n = level; }
+        BZW_COUNT(BZC_STAGE_A, tested * __popc(__ballot_sync(0xffffffffu, live)));
         continue;
       }
 
@@ -452,6 +466,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
         const uint32_t n = min(qa, 32u);
         const uint32_t q = qa - n + lane;
         if(lane == 0u) { P.qa_n = qa - n; }
+        BZW_COUNT(BZC_STAGE_A, n);
         if(lane < n) {
           const uint32_t slot = P.qa_slot[q];
           bz_cull_rec c;
@@ -460,7 +475,6 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           const bzv3 s = bz_v(P.ray[0][slot], P.ray[1][slot], P.ray[2][slot]);
           const bzv3 d = bz_v(P.ray[3][slot], P.ray[4][slot], P.ray[5][slot]);
           float cosine, distance;
-          ++c_a;
           if(bz_stage_a(c, s, d, true, cosine, distance)) {
             const uint32_t at = atomicAdd(&P.qb_n, 1u);
             P.qb_patch[at] = patch;
@@ -489,6 +503,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
         unsigned long long key = BZ_KEY_NONE;
         bz_hit hit;
         hit.what = BZ_MISS;
+        bool evaluated = false;
         if(lane < n) {
           bz_cull_rec c;
           uint32_t index;
@@ -496,12 +511,11 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           const bzv3 s = bz_v(P.ray[0][slot], P.ray[1][slot], P.ray[2][slot]);
           const bzv3 d = bz_v(P.ray[3][slot], P.ray[4][slot], P.ray[5][slot]);
           float cosine, distance;
-          if(!first_level) { ++c_a; }
           if(bz_stage_a(c, s, d, first_level, cosine, distance)) {
             bz_newton_rec t;
             bzw_load_newton(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
             bz_stage_b(c, t, s, d, cosine, distance, hit);
-            ++c_b;
+            evaluated = true;
             if(hit.what <= BZ_FOLLOW2) {
               if(first_level) {                // one hop, no recursion (bezierMesh.cpp:213-217)
                 const uint32_t at = atomicAdd(&P.qb_n, 1u);
@@ -517,6 +531,8 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           }
         }
         __syncwarp();
+        BZW_COUNT(BZC_STAGE_A, __popc(__ballot_sync(0xffffffffu, lane < n && !first_level)));
+        BZW_COUNT(BZC_STAGE_B, __popc(__ballot_sync(0xffffffffu, evaluated)));
         if(key != BZ_KEY_NONE && P.best[slot] == key) {
           P.pay[0][slot] = hit.point.x;  P.pay[1][slot] = hit.point.y;  P.pay[2][slot] = hit.point.z;
           P.pay[3][slot] = hit.normal.x; P.pay[4][slot] = hit.normal.y; P.pay[5][slot] = hit.normal.z;
@@ -530,11 +546,12 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
 
     // ================= resolve: nearest hit -> Snell -> expected-side check -> next bounce or finish =================
     __syncwarp();
-#pragma unroll
+#pragma unroll 1
     for(int g = 0; g < BZ_GROUPS; ++g) {
       const uint32_t slot = (uint32_t)g * 32u + lane;
       const uint32_t st = P.state[slot];
-      if((st & 1u) == 0u) { continue; }
+      uint32_t events = 0u;                  // bit 0 Snell block reached, 1 entered, 2 exited, 3 lost
+      if((st & 1u) != 0u) {
       uint32_t expected = (st >> 1) & 3u;
       uint32_t crossings = st >> 4;
       const unsigned long long key = P.best[slot];
@@ -570,13 +587,13 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
         bzv3 refracted = d;
         if(found) {
           status = bz_snell(T.ri, hit.cos_incidence, hit.normal, refracted);
-          ++c_snell;
+          events |= 1u;
         }
         status = (status == expected) ? status : BZ_STATUS_NONE;
         if(status != BZ_STATUS_NONE) {
           s = hit.point;
           d = refracted;
-          if(status == BZ_STATUS_INSIDE) { ++c_enter; } else { ++c_exit; }
+          events |= (status == BZ_STATUS_INSIDE) ? 2u : 4u;
         }
         if(JOB == BZ_JOB_REFRACT) {
           const unsigned long long ray_id = ((unsigned long long)P.id_hi[slot] << 32) | P.id_lo[slot];
@@ -600,7 +617,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             }
             else {                                  // entered and never left
               value = J.scene.value_lost;
-              ++c_lost;
+              events |= 8u;
             }
             atomicAdd(J.accum + P.id_lo[slot], value);
             live = false;
@@ -612,21 +629,19 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
         }
       }
       P.state[slot] = live ? (1u | (expected << 1) | (crossings << 4)) : 0u;
+      }
+      if(JOB != BZ_JOB_INTERSECT) {
+        BZW_COUNT(BZC_SNELL, __popc(__ballot_sync(0xffffffffu, (events & 1u) != 0u)));
+        BZW_COUNT(BZC_ENTER, __popc(__ballot_sync(0xffffffffu, (events & 2u) != 0u)));
+        BZW_COUNT(BZC_EXIT, __popc(__ballot_sync(0xffffffffu, (events & 4u) != 0u)));
+        BZW_COUNT(BZC_LOST, __popc(__ballot_sync(0xffffffffu, (events & 8u) != 0u)));
+      }
     }
   }
 
-  // ---- work counters: warp reduce, one atomic per warp and counter ----
-  if(J.stats != nullptr) {
-    unsigned long long v[BZ_NSTAT] = { c_primary, c_calls, c_a, (unsigned long long)c_b, (unsigned long long)c_snell,
-                                       (unsigned long long)c_enter, (unsigned long long)c_exit, (unsigned long long)c_lost, c_nodes,
-                                       (unsigned long long)c_pnodes, (unsigned long long)c_pwalks, (unsigned long long)c_lwalks };
-#pragma unroll
-    for(int i = 0; i < BZ_NSTAT; ++i) {
-      unsigned long long x = v[i];
-      for(int o = 16; o > 0; o >>= 1) { x += __shfl_down_sync(0xffffffffu, x, o); }
-      if(lane == 0u && x != 0ull) { atomicAdd(J.stats + i, x); }
-    }
-  }
+  // ---- work counters: one atomic per warp and counter ----
+  __syncwarp();
+  if(J.stats != nullptr && lane < BZ_NSTAT && P.count[lane] != 0ull) { atomicAdd(J.stats + lane, P.count[lane]); }
 }
 
 cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream) {
