@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -217,11 +218,28 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
     grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * 2u, wanted);
   }
   else {
-    // persistent grid: every resident CTA slot of the device, or fewer when the batch is small
+    // tiles of the job: RENDER: square pixel blocks of about 1024 rays (side a power of two); batches: 1024 consecutive rays
+    if(job == BZ_JOB_RENDER) {
+      uint32_t const spp = desc.camera.strata * desc.camera.strata;
+      uint32_t side = 32u;
+      while(side > 2u && (uint64_t)side * side * spp > 1536u) { side /= 2u; }
+      if((uint64_t)side * side * spp >= (1ull << 31)) { return bz_fail(BZ_ERR_INVALID, "too many samples per pixel"); }
+      desc.tile_side = side;
+      desc.tile_rays = side * side * spp;
+      desc.tiles_x = (desc.camera.width + side - 1u) / side;
+      desc.tile_count = (uint64_t)desc.tiles_x * ((desc.rows + side - 1u) / side);
+    }
+    else {
+      desc.tile_side = 0u;
+      desc.tile_rays = 1024u;
+      desc.tiles_x = 0u;
+      desc.tile_count = (desc.ray_count + 1023u) / 1024u;
+    }
+    if(desc.tile_count >= 0xffffffffull) { return bz_fail(BZ_ERR_INVALID, "job too large"); }
+    // persistent grid: every resident CTA slot of the device, or fewer when the job has fewer tiles
     int perSm = 0, raysPerCta = 0;
     BZ_CUDA(bz_warp_trace_occupancy(&perSm, &raysPerCta));
-    uint64_t const wanted = (desc.ray_count + (uint64_t)raysPerCta - 1u) / (uint64_t)raysPerCta;
-    grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * (uint64_t)std::max(perSm, 1), wanted);
+    grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * (uint64_t)std::max(perSm, 1), desc.tile_count);
   }
   BZ_CUDA(cudaEventRecord(lens->ev_begin, stream));
   if(brute) { BZ_CUDA(bz_launch_trace(job, true, lens->tables, desc, grid, stream)); }
@@ -260,6 +278,7 @@ static int bz_render_common(bz_lens *lens, const bz_camera *camera, const bz_sce
   desc.camera = *camera;
   desc.scene = *scene;
   desc.row0 = row0;
+  desc.rows = rows;
   desc.stripe_rows = stripe_rows;
   desc.stripe_rank = rank;
   desc.stripe_ranks = ranks;

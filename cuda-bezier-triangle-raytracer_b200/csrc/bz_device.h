@@ -72,7 +72,13 @@ struct bz_job {
   float    *out_bary;
   // all
   uint64_t  ray_count;       // primary rays of this call
-  unsigned long long *next_ray;   // work counter, zeroed before launch
+  // work distribution: the job is cut into tiles handed to CTAs; RENDER: square blocks of tile_side x tile_side pixels
+  // (tile_side a power of two, pixels of a tile in Morton order, tile_rays = tile_side^2 * spp); batch jobs: tile_rays
+  // consecutive rays
+  uint32_t  rows;            // RENDER: image rows of this call (local rows of the band)
+  uint32_t  tile_side, tile_rays, tiles_x;
+  uint64_t  tile_count;
+  unsigned long long *next_ray;   // tile counter, zeroed before launch
   unsigned long long *stats;      // 9 counters in bz_stats order, accumulated; nullable
 };
 

@@ -36,9 +36,11 @@
 #ifndef BZ_GROUPS
 #define BZ_GROUPS    1
 #endif
-#define BZ_WARPS     4
+#ifndef BZ_WARPS
+#define BZ_WARPS     16      // one CTA per SM: its warps share tiles of the job (L1 locality), never a barrier
+#endif
 #ifndef BZ_MIN_CTAS
-#define BZ_MIN_CTAS  4
+#define BZ_MIN_CTAS  1
 #endif
 #define BZ_SLOTS     (32 * BZ_GROUPS)
 #ifndef BZ_WALK_BURST
@@ -168,38 +170,73 @@ __device__ __forceinline__ float bzw_warp_max(float v) { float r; asm volatile("
 
 // One axis of the packet's interval slab test.  Every ray of the packet has origin o in [o_lo, o_hi] and direction d in
 // [d_lo, d_hi] on this axis, so for t >= 0 its coordinate lies in [o_lo + t d_lo, o_hi + t d_hi]; it can be inside the
-// slab [lo - m, hi + m] only if   o_lo + t d_lo <= hi + m   and   o_hi + t d_hi >= lo - m.   Each is one bound on t whose
-// kind (upper / lower) follows from the sign of d_lo resp. d_hi, the same for all boxes.
+// slab [lo - m, hi + m] only if   (1) o_lo + t d_lo <= hi + m   and   (2) o_hi + t d_hi >= lo - m.   Each is one bound on
+// t whose kind follows from the sign of d_lo resp. d_hi, the same for all boxes:
+//   d_lo > 0 (all rays ascend):   (2) bounds t from below, (1) from above
+//   d_hi < 0 (all rays descend):  (1) bounds t from below, (2) from above
+//   d_lo < 0 < d_hi (straddle):   both bound t from below, nothing from above
+// The three cases become ONE select-free formula by choosing per packet which box face each term reads (an address
+// offset) and by neutral coefficients (0, -inf) / (0, +inf):
+//   near = max(face_n * in + cn, face_f * ix + cx),  far = face_f * jf + cf
 struct bzw_axis {
-  float inv1, c1, inv2, c2;     // t1 = hi * inv1 + c1,  t2 = lo * inv2 + c2
-  bool  upper1, lower2;         // t1 is an upper bound (d_lo > 0), else a lower one; t2 is a lower bound (d_hi > 0), else an upper one
+  float in, cn, ix, cx, jf, cf;
+  uint32_t off_n, off_f;        // word offsets of the two faces from the axis's lo[] row of a packet node: 0 (lo) or 96 (hi)
 };
 
 __device__ __forceinline__ bzw_axis bzw_make_axis(float o_lo, float o_hi, float d_lo, float d_hi, float margin) {
-  bzw_axis a;
+  const float inf = __int_as_float(0x7f800000);
   // a vanishing slope is pushed to the permissive side (the lane walk treats |d| < 1e-20 the same way)
   if(fabsf(d_lo) < 1e-20f) { d_lo = -1e-20f; }
   if(fabsf(d_hi) < 1e-20f) { d_hi = 1e-20f; }
-  a.inv1 = 1.0f / d_lo;
-  a.inv2 = 1.0f / d_hi;
-  a.c1 = (margin - o_lo) * a.inv1;
-  a.c2 = (-margin - o_hi) * a.inv2;
-  a.upper1 = d_lo > 0.0f;
-  a.lower2 = d_hi > 0.0f;
+  const float inv1 = 1.0f / d_lo, inv2 = 1.0f / d_hi;
+  const float c1 = (margin - o_lo) * inv1;          // (1): t1 = hi * inv1 + c1
+  const float c2 = (-margin - o_hi) * inv2;         // (2): t2 = lo * inv2 + c2
+  bzw_axis a;
+  if(d_lo > 0.0f)      { a.off_n = 0u;  a.in = inv2; a.cn = c2; a.off_f = 96u; a.jf = inv1; a.cf = c1;  a.ix = 0.0f; a.cx = -inf; }
+  else if(d_hi < 0.0f) { a.off_n = 96u; a.in = inv1; a.cn = c1; a.off_f = 0u;  a.jf = inv2; a.cf = c2;  a.ix = 0.0f; a.cx = -inf; }
+  else                 { a.off_n = 0u;  a.in = inv2; a.cn = c2; a.off_f = 96u; a.jf = 0.0f; a.cf = inf; a.ix = inv1; a.cx = c1; }
   return a;
 }
 
-__device__ __forceinline__ void bzw_axis_bounds(const bzw_axis &a, float lo, float hi, float &tnear, float &tfar) {
-  const float inf = __int_as_float(0x7f800000);
-  const float t1 = __fmaf_rn(hi, a.inv1, a.c1), t2 = __fmaf_rn(lo, a.inv2, a.c2);
-  tnear = fmaxf(tnear, fmaxf(a.upper1 ? -inf : t1, a.lower2 ? t2 : -inf));
-  tfar = fminf(tfar, fminf(a.upper1 ? t1 : inf, a.lower2 ? inf : t2));
+__device__ __forceinline__ void bzw_axis_bounds(const bzw_axis &a, const float *row, float &tnear, float &tfar) {
+  const float face_n = __ldg(row + a.off_n), face_f = __ldg(row + a.off_f);
+  tnear = fmaxf(tnear, fmaxf(__fmaf_rn(face_n, a.in, a.cn), __fmaf_rn(face_f, a.ix, a.cx)));
+  tfar = fminf(tfar, __fmaf_rn(face_f, a.jf, a.cf));
+}
+
+// ---- work distribution: tiles of the job from a global counter per CTA, packets of a tile from shared memory per warp ----
+// cta_work = tile << 32 | rays of the tile handed out so far.  The warp whose packet is the first one past the end of the
+// tile fetches the next tile (and takes its first packet); warps arriving in between wait for the tile number to change.
+__device__ __forceinline__ unsigned long long bzw_take_packet(unsigned long long *cta_work, const bz_job &J) {
+  for(;;) {
+    const unsigned long long w = atomicAdd(cta_work, 32ull);
+    const uint32_t tile = (uint32_t)(w >> 32), at = (uint32_t)w;
+    if(tile == BZ_END || at < J.tile_rays) { return w; }
+    if(at < J.tile_rays + 32u) {
+      const unsigned long long next = atomicAdd(J.next_ray, 1ull);
+      const unsigned long long fresh = ((next < J.tile_count) ? next : (unsigned long long)BZ_END) << 32;
+      atomicExch(cta_work, fresh | 32ull);
+      return fresh;
+    }
+    while((uint32_t)(*(volatile unsigned long long*)cta_work >> 32) == tile) { __nanosleep(64); }
+  }
+}
+
+// the even bits of v, compacted: x of a Morton index (y = bzw_even_bits(v >> 1))
+__device__ __forceinline__ uint32_t bzw_even_bits(uint32_t v) {
+  v &= 0x55555555u;
+  v = (v | (v >> 1)) & 0x33333333u;
+  v = (v | (v >> 2)) & 0x0f0f0f0fu;
+  v = (v | (v >> 4)) & 0x00ff00ffu;
+  v = (v | (v >> 8)) & 0x0000ffffu;
+  return v;
 }
 
 template<int JOB>
 __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kernel(const bz_tables T, const bz_job J) {
-  __shared__ bz_warp_pool pools[BZ_WARPS];
-  bz_warp_pool &P = pools[threadIdx.x >> 5];
+  extern __shared__ __align__(16) unsigned char bzw_shared[];
+  bz_warp_pool &P = reinterpret_cast<bz_warp_pool*>(bzw_shared)[threadIdx.x >> 5];
+  __shared__ unsigned long long cta_work;    // tile of the job this CTA is working on << 32 | rays of it handed out
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t spp = J.camera.strata * J.camera.strata;
   const uint32_t direct_end = T.always_first + T.always_count;
@@ -209,6 +246,11 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
   for(int g = 0; g < BZ_GROUPS; ++g) { P.state[g * 32 + lane] = 0u; }
   if(lane == 0u) { P.qa_n = 0u; P.qb_n = 0u; }
   if(lane < BZ_NSTAT) { P.count[lane] = 0ull; }
+  if(threadIdx.x == 0u) {
+    const unsigned long long first = atomicAdd(J.next_ray, 1ull);
+    cta_work = ((first < J.tile_count) ? first : (unsigned long long)BZ_END) << 32;
+  }
+  __syncthreads();                           // the only CTA barrier of the kernel
   __syncwarp();
 
   for(;;) {
@@ -240,46 +282,49 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           uint32_t st = P.state[slot];
           bool live = (st & 1u) != 0u;
           const uint32_t dead = __ballot_sync(0xffffffffu, !live);
-#ifdef BZ_REFILL_PARTIAL
-          const uint32_t need = dead;
-#else
           const uint32_t need = (dead == 0xffffffffu) ? dead : 0u;
-#endif
-          if(need != 0u && !exhausted) {
-            unsigned long long base = 0ull;
-            const int leader = __ffs(need) - 1;
-            if((int)lane == leader) { base = atomicAdd(J.next_ray, (unsigned long long)__popc(need)); }
-            base = __shfl_sync(0xffffffffu, base, leader);
-            exhausted = (base + (unsigned long long)__popc(need) >= J.ray_count);
-            if(!live) {
-              const unsigned long long id = base + (unsigned long long)__popc(need & ((1u << lane) - 1u));
-              if(id < J.ray_count) {
-                bzv3 s, d;
-                uint32_t expected = BZ_STATUS_INSIDE;
-                if(JOB == BZ_JOB_RENDER) {
-                  const uint32_t pixel = (uint32_t)(id / spp);
-                  const uint32_t sample = (uint32_t)(id - (unsigned long long)pixel * spp);
-                  const uint32_t row = pixel / J.camera.width;
-                  const uint32_t px = pixel - row * J.camera.width;
-                  const uint32_t py = (J.stripe_rows == 0u) ? J.row0 + row
-                                    : ((row / J.stripe_rows) * J.stripe_ranks + J.stripe_rank) * J.stripe_rows + row % J.stripe_rows;
-                  bzw_primary_ray(J.camera, px, py, sample % J.camera.strata, sample / J.camera.strata, s, d);
-                  P.id_lo[slot] = pixel;
-                }
-                else {
-                  s = bz_v(J.in_start[id * 3u], J.in_start[id * 3u + 1u], J.in_start[id * 3u + 2u]);
-                  d = bz_v(J.in_dir[id * 3u], J.in_dir[id * 3u + 1u], J.in_dir[id * 3u + 2u]);
-                  expected = (JOB == BZ_JOB_REFRACT) ? (J.in_expected[id] & 3u) : 0u;
-                  P.id_lo[slot] = (uint32_t)id;
-                  P.id_hi[slot] = (uint32_t)(id >> 32);
-                }
-                P.ray[0][slot] = s.x; P.ray[1][slot] = s.y; P.ray[2][slot] = s.z;
-                P.ray[3][slot] = d.x; P.ray[4][slot] = d.y; P.ray[5][slot] = d.z;
-                st = 1u | (expected << 1);
-                P.state[slot] = st;
-                live = true;
+          while(need != 0u && !exhausted) {
+            // the CTA's warps share one tile of the job (a square block of pixels, or 1024 consecutive batch rays), so
+            // the 16 warps of an SM work next to each other and meet the same hierarchy nodes and patch records in L1
+            unsigned long long w = 0ull;
+            if(lane == 0u) { w = bzw_take_packet(&cta_work, J); }
+            w = __shfl_sync(0xffffffffu, w, 0);
+            const uint32_t tile = (uint32_t)(w >> 32), at = (uint32_t)w + lane;
+            if(tile == BZ_END) { exhausted = true; break; }
+            bool valid = at < J.tile_rays;
+            bzv3 s, d;
+            uint32_t expected = BZ_STATUS_INSIDE;
+            if(JOB == BZ_JOB_RENDER) {
+              const uint32_t inside = at / spp, sample = at - inside * spp;              // pixel of the tile in Morton order, sample of the pixel
+              const uint32_t tile_y = tile / J.tiles_x, tile_x = tile - tile_y * J.tiles_x;
+              const uint32_t px = tile_x * J.tile_side + bzw_even_bits(inside), row = tile_y * J.tile_side + bzw_even_bits(inside >> 1);
+              valid = valid && px < J.camera.width && row < J.rows;
+              if(valid) {
+                const uint32_t py = (J.stripe_rows == 0u) ? J.row0 + row
+                                  : ((row / J.stripe_rows) * J.stripe_ranks + J.stripe_rank) * J.stripe_rows + row % J.stripe_rows;
+                bzw_primary_ray(J.camera, px, py, sample % J.camera.strata, sample / J.camera.strata, s, d);
+                P.id_lo[slot] = row * J.camera.width + px;
               }
             }
+            else {
+              const unsigned long long id = (unsigned long long)tile * J.tile_rays + at;
+              valid = valid && id < J.ray_count;
+              if(valid) {
+                s = bz_v(J.in_start[id * 3u], J.in_start[id * 3u + 1u], J.in_start[id * 3u + 2u]);
+                d = bz_v(J.in_dir[id * 3u], J.in_dir[id * 3u + 1u], J.in_dir[id * 3u + 2u]);
+                expected = (JOB == BZ_JOB_REFRACT) ? (J.in_expected[id] & 3u) : 0u;
+                P.id_lo[slot] = (uint32_t)id;
+                P.id_hi[slot] = (uint32_t)(id >> 32);
+              }
+            }
+            if(valid) {
+              P.ray[0][slot] = s.x; P.ray[1][slot] = s.y; P.ray[2][slot] = s.z;
+              P.ray[3][slot] = d.x; P.ray[4][slot] = d.y; P.ray[5][slot] = d.z;
+              st = 1u | (expected << 1);
+              P.state[slot] = st;
+              live = true;
+            }
+            if(__ballot_sync(0xffffffffu, valid) != 0u) { break; }      // (a packet of an edge tile may lie outside the image)
           }
           P.best[slot] = BZ_KEY_NONE;
           const uint32_t live_mask = __ballot_sync(0xffffffffu, live);
@@ -319,13 +364,11 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             while(packet_done && sp != 0u) {
               --sp;
               const float *box = T.packet + (size_t)P.stack[sp] * 224u + lane;
-              const float lox = __ldg(box), loy = __ldg(box + 32), loz = __ldg(box + 64);
-              const float hix = __ldg(box + 96), hiy = __ldg(box + 128), hiz = __ldg(box + 160);
               const uint32_t code = __float_as_uint(__ldg(box + 192));
               float tnear = 0.0f, tfar = inf;
-              bzw_axis_bounds(ax, lox, hix, tnear, tfar);
-              bzw_axis_bounds(ay, loy, hiy, tnear, tfar);
-              bzw_axis_bounds(az, loz, hiz, tnear, tfar);
+              bzw_axis_bounds(ax, box, tnear, tfar);
+              bzw_axis_bounds(ay, box + 32, tnear, tfar);
+              bzw_axis_bounds(az, box + 64, tnear, tfar);
               const bool hit = (code != 0u) && (tnear <= tfar);
               const bool inner = (code & 0x80000000u) != 0u;
               const uint32_t hit_inner = __ballot_sync(0xffffffffu, hit && inner);
@@ -438,11 +481,25 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
         const uint32_t below = (1u << lane) - 1u;
         uint32_t level = qb;                  // warp-uniform copy of the level of queue B
         uint32_t tested = 0u;
+        // software pipeline: the record of the next turn is in flight while this turn's record is tested
+        float4 r0, r1, r2, r3;
+        {
+          const float4 *rec = T.leaf + (size_t)((P.cand[cand_at] >> 3) + cand_sub) * BZ_CULL_F4;     // one address for the warp: broadcast loads
+          r0 = __ldg(rec); r1 = __ldg(rec + 1); r2 = __ldg(rec + 2); r3 = __ldg(rec + 3);
+        }
         while(cand_at < cand_n && level <= BZ_QB_CAP - 64u) {
-          const uint32_t code = P.cand[cand_at];
+          const float4 c0 = r0, c1 = r1, c2 = r2, c3 = r3;
+          if(++cand_sub == (P.cand[cand_at] & 7u)) { cand_sub = 0u; ++cand_at; }
+          if(cand_at < cand_n) {
+            const float4 *rec = T.leaf + (size_t)((P.cand[cand_at] >> 3) + cand_sub) * BZ_CULL_F4;
+            r0 = __ldg(rec); r1 = __ldg(rec + 1); r2 = __ldg(rec + 2); r3 = __ldg(rec + 3);
+          }
           bz_cull_rec c;
-          uint32_t patch;
-          bzw_unpack_cull(T.leaf + (size_t)((code >> 3) + cand_sub) * BZ_CULL_F4, c, patch);     // one address for the warp: a broadcast load
+          c.n = bz_v(c0.x, c0.y, c0.z); c.k = c0.w;
+          c.b0 = bz_v(c1.x, c1.y, c1.z); c.h_in = c1.w;
+          c.b1 = bz_v(c2.x, c2.y, c2.z); c.h_out = c2.w;
+          c.b2 = bz_v(c3.x, c3.y, c3.z);
+          const uint32_t patch = __float_as_uint(c3.w);
           float cosine, distance;
           const bool pass = live && bz_stage_a(c, s, d, true, cosine, distance);
           const uint32_t passed = __ballot_sync(0xffffffffu, pass);
@@ -454,7 +511,6 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           }
           level += __popc(passed);
           ++tested;
-          if(++cand_sub == (code & 7u)) { cand_sub = 0u; ++cand_at; }
         }
         if(lane == 0u) { P.qb_n = level; }
         BZW_COUNT(BZC_STAGE_A, tested * __popc(__ballot_sync(0xffffffffu, live)));
@@ -644,15 +700,35 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
   if(J.stats != nullptr && lane < BZ_NSTAT && P.count[lane] != 0ull) { atomicAdd(J.stats + lane, P.count[lane]); }
 }
 
+static size_t bzw_shared_bytes() { return sizeof(bz_warp_pool) * BZ_WARPS; }
+
+static cudaError_t bzw_configure() {
+  static bool done[64] = {};                 // the attribute is per device
+  int device = 0;
+  cudaError_t e = cudaGetDevice(&device);
+  if(e != cudaSuccess) { return e; }
+  bool &configured = done[device & 63];
+  if(configured) { return cudaSuccess; }
+  e = cudaFuncSetAttribute(bz_warp_trace_kernel<BZ_JOB_RENDER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bzw_shared_bytes());
+  if(e == cudaSuccess) { e = cudaFuncSetAttribute(bz_warp_trace_kernel<BZ_JOB_REFRACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bzw_shared_bytes()); }
+  if(e == cudaSuccess) { e = cudaFuncSetAttribute(bz_warp_trace_kernel<BZ_JOB_INTERSECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bzw_shared_bytes()); }
+  configured = (e == cudaSuccess);
+  return e;
+}
+
 cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream) {
-  if(job == BZ_JOB_RENDER) { bz_warp_trace_kernel<BZ_JOB_RENDER><<<grid, 32 * BZ_WARPS, 0, stream>>>(tables, desc); }
-  else if(job == BZ_JOB_REFRACT) { bz_warp_trace_kernel<BZ_JOB_REFRACT><<<grid, 32 * BZ_WARPS, 0, stream>>>(tables, desc); }
-  else { bz_warp_trace_kernel<BZ_JOB_INTERSECT><<<grid, 32 * BZ_WARPS, 0, stream>>>(tables, desc); }
+  cudaError_t e = bzw_configure();
+  if(e != cudaSuccess) { return e; }
+  if(job == BZ_JOB_RENDER) { bz_warp_trace_kernel<BZ_JOB_RENDER><<<grid, 32 * BZ_WARPS, bzw_shared_bytes(), stream>>>(tables, desc); }
+  else if(job == BZ_JOB_REFRACT) { bz_warp_trace_kernel<BZ_JOB_REFRACT><<<grid, 32 * BZ_WARPS, bzw_shared_bytes(), stream>>>(tables, desc); }
+  else { bz_warp_trace_kernel<BZ_JOB_INTERSECT><<<grid, 32 * BZ_WARPS, bzw_shared_bytes(), stream>>>(tables, desc); }
   return cudaGetLastError();
 }
 
-// resident CTAs per SM of the render instantiation (the persistent grid is sized from it), rays per CTA pass
+// resident CTAs per SM of the render instantiation (the persistent grid is sized from it)
 cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta) {
   *out_rays_per_cta = BZ_WARPS * BZ_SLOTS;
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(out_ctas_per_sm, bz_warp_trace_kernel<BZ_JOB_RENDER>, 32 * BZ_WARPS, 0);
+  cudaError_t e = bzw_configure();
+  if(e != cudaSuccess) { return e; }
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(out_ctas_per_sm, bz_warp_trace_kernel<BZ_JOB_RENDER>, 32 * BZ_WARPS, bzw_shared_bytes());
 }
