@@ -223,6 +223,7 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
       uint32_t const spp = desc.camera.strata * desc.camera.strata;
       uint32_t side = 32u;
       while(side > 2u && (uint64_t)side * side * spp > 1536u) { side /= 2u; }
+      if(const char *env = std::getenv("BZ_B200_TILE")) { side = (uint32_t)std::max(2, std::atoi(env)); }     // tuning runs only (power of two)
       if((uint64_t)side * side * spp >= (1ull << 31)) { return bz_fail(BZ_ERR_INVALID, "too many samples per pixel"); }
       desc.tile_side = side;
       desc.tile_rays = side * side * spp;

@@ -481,37 +481,39 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
         const uint32_t below = (1u << lane) - 1u;
         uint32_t level = qb;                  // warp-uniform copy of the level of queue B
         uint32_t tested = 0u;
-        // software pipeline: the record of the next turn is in flight while this turn's record is tested
-        float4 r0, r1, r2, r3;
-        {
-          const float4 *rec = T.leaf + (size_t)((P.cand[cand_at] >> 3) + cand_sub) * BZ_CULL_F4;     // one address for the warp: broadcast loads
-          r0 = __ldg(rec); r1 = __ldg(rec + 1); r2 = __ldg(rec + 2); r3 = __ldg(rec + 3);
-        }
+        // all addresses are the same for the whole warp (broadcast loads); no software pipelining: holding a second record
+        // in registers costs more in spills around stage B than the L1 latency it hides
+        float4 a0, a1, a2, a3;
+#define BZW_FETCH(r0, r1, r2, r3) { \
+          const float4 *rec = T.leaf + (size_t)((P.cand[cand_at] >> 3) + cand_sub) * BZ_CULL_F4; \
+          r0 = __ldg(rec); r1 = __ldg(rec + 1); r2 = __ldg(rec + 2); r3 = __ldg(rec + 3); }
+#define BZW_ADVANCE() { if(++cand_sub == (P.cand[cand_at] & 7u)) { cand_sub = 0u; ++cand_at; } }
+#define BZW_TEST(r0, r1, r2, r3) { \
+          bz_cull_rec c; \
+          c.n = bz_v(r0.x, r0.y, r0.z); c.k = r0.w; \
+          c.b0 = bz_v(r1.x, r1.y, r1.z); c.h_in = r1.w; \
+          c.b1 = bz_v(r2.x, r2.y, r2.z); c.h_out = r2.w; \
+          c.b2 = bz_v(r3.x, r3.y, r3.z); \
+          const uint32_t patch = __float_as_uint(r3.w); \
+          float cosine, distance; \
+          const bool pass = live && bz_stage_a(c, s, d, true, cosine, distance); \
+          const uint32_t passed = __ballot_sync(0xffffffffu, pass); \
+          if(pass) { \
+            const uint32_t at = level + __popc(passed & below); \
+            P.qb_patch[at] = patch; \
+            P.qb_loop[at] = patch; \
+            P.qb_slot[at] = (uint8_t)(slot | 0x80u); \
+          } \
+          level += __popc(passed); \
+          ++tested; }
         while(cand_at < cand_n && level <= BZ_QB_CAP - 64u) {
-          const float4 c0 = r0, c1 = r1, c2 = r2, c3 = r3;
-          if(++cand_sub == (P.cand[cand_at] & 7u)) { cand_sub = 0u; ++cand_at; }
-          if(cand_at < cand_n) {
-            const float4 *rec = T.leaf + (size_t)((P.cand[cand_at] >> 3) + cand_sub) * BZ_CULL_F4;
-            r0 = __ldg(rec); r1 = __ldg(rec + 1); r2 = __ldg(rec + 2); r3 = __ldg(rec + 3);
-          }
-          bz_cull_rec c;
-          c.n = bz_v(c0.x, c0.y, c0.z); c.k = c0.w;
-          c.b0 = bz_v(c1.x, c1.y, c1.z); c.h_in = c1.w;
-          c.b1 = bz_v(c2.x, c2.y, c2.z); c.h_out = c2.w;
-          c.b2 = bz_v(c3.x, c3.y, c3.z);
-          const uint32_t patch = __float_as_uint(c3.w);
-          float cosine, distance;
-          const bool pass = live && bz_stage_a(c, s, d, true, cosine, distance);
-          const uint32_t passed = __ballot_sync(0xffffffffu, pass);
-          if(pass) {
-            const uint32_t at = level + __popc(passed & below);
-            P.qb_patch[at] = patch;
-            P.qb_loop[at] = patch;
-            P.qb_slot[at] = (uint8_t)(slot | 0x80u);
-          }
-          level += __popc(passed);
-          ++tested;
+          BZW_FETCH(a0, a1, a2, a3)
+          BZW_ADVANCE()
+          BZW_TEST(a0, a1, a2, a3)
         }
+#undef BZW_FETCH
+#undef BZW_ADVANCE
+#undef BZW_TEST
         if(lane == 0u) { P.qb_n = level; }
         BZW_COUNT(BZC_STAGE_A, tested * __popc(__ballot_sync(0xffffffffu, live)));
         continue;
@@ -575,7 +577,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             if(hit.what <= BZ_FOLLOW2) {
               if(first_level) {                // one hop, no recursion (bezierMesh.cpp:213-217)
                 const uint32_t at = atomicAdd(&P.qb_n, 1u);
-                P.qb_patch[at] = t.nb[hit.what];
+                P.qb_patch[at] = (hit.what == BZ_FOLLOW0) ? t.nb[0] : ((hit.what == BZ_FOLLOW1) ? t.nb[1] : t.nb[2]);     // (no dynamic index: keeps the record in registers)
                 P.qb_loop[at] = loop;
                 P.qb_slot[at] = (uint8_t)slot;
               }
