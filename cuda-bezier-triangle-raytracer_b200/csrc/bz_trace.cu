@@ -95,22 +95,26 @@ __device__ __forceinline__ void bzw_unpack_cull(const float4 *p, bz_cull_rec &c,
   index = __float_as_uint(r3.w);
 }
 
-__device__ __forceinline__ void bzw_load_newton(const float4 *p, bz_newton_rec &t) {
-  float w[48];
+// control points and dirB: words 0..32 of the stage-B record (word 33..35 of float4 #8 are the first divider normal)
+__device__ __forceinline__ void bzw_load_newton_root(const float4 *p, bz_newton_rec &t) {
+  float w[36];
 #pragma unroll
-  for(int i = 0; i < BZ_NEWTON_F4; ++i) {
+  for(int i = 0; i < 9; ++i) {
     float4 r = __ldg(p + i);
     w[4 * i] = r.x; w[4 * i + 1] = r.y; w[4 * i + 2] = r.z; w[4 * i + 3] = r.w;
   }
 #pragma unroll
   for(int i = 0; i < 10; ++i) { t.cp[i] = bz_v(w[3 * i], w[3 * i + 1], w[3 * i + 2]); }
   t.dir_b = bz_v(w[30], w[31], w[32]);
-#pragma unroll
-  for(int i = 0; i < 3; ++i) {
-    t.div_n[i] = bz_v(w[33 + 4 * i], w[34 + 4 * i], w[35 + 4 * i]);
-    t.div_k[i] = w[36 + 4 * i];
-    t.nb[i] = __float_as_uint(w[45 + i]);
-  }
+}
+
+// divider planes and neighbours: words 33..47, fetched after the root search (they are not live across its loop)
+__device__ __forceinline__ void bzw_load_newton_side(const float4 *p, bz_newton_rec &t) {
+  const float4 carry = __ldg(p + 8), r9 = __ldg(p + 9), r10 = __ldg(p + 10), r11 = __ldg(p + 11);
+  t.div_n[0] = bz_v(carry.y, carry.z, carry.w); t.div_k[0] = r9.x;
+  t.div_n[1] = bz_v(r9.y, r9.z, r9.w);          t.div_k[1] = r10.x;
+  t.div_n[2] = bz_v(r10.y, r10.z, r10.w);       t.div_k[2] = r11.x;
+  t.nb[0] = __float_as_uint(r11.y); t.nb[1] = __float_as_uint(r11.z); t.nb[2] = __float_as_uint(r11.w);
 }
 
 // K1: primary ray of sample (px, py, sx, sy); definitions in include/bz_capi.h (bz_camera).
@@ -571,8 +575,11 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           float cosine, distance;
           if(bz_stage_a(c, s, d, first_level, cosine, distance)) {
             bz_newton_rec t;
-            bzw_load_newton(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
-            bz_stage_b(c, t, s, d, cosine, distance, hit);
+            bzw_load_newton_root(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
+            if(bz_stage_b_root(c, t, s, d, cosine, distance, hit)) {
+              bzw_load_newton_side(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
+              bz_stage_b_side(t, d, hit);
+            }
             evaluated = true;
             if(hit.what <= BZ_FOLLOW2) {
               if(first_level) {                // one hop, no recursion (bezierMesh.cpp:213-217)
