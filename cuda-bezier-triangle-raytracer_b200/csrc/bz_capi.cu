@@ -180,7 +180,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
 }
 
 int bz_lens_set_mode(bz_lens *lens, uint32_t mode) {
-  if(lens == nullptr || mode > BZ_MODE_CULLED) { return bz_fail(BZ_ERR_INVALID, "bad lens or mode"); }
+  if(lens == nullptr || mode > BZ_MODE_LANES) { return bz_fail(BZ_ERR_INVALID, "bad lens or mode"); }
   lens->mode = mode;
   return BZ_OK;
 }
@@ -244,7 +244,11 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
   }
   BZ_CUDA(cudaEventRecord(lens->ev_begin, stream));
   if(brute) { BZ_CUDA(bz_launch_trace(job, true, lens->tables, desc, grid, stream)); }
-  else { BZ_CUDA(bz_launch_warp_trace(job, lens->tables, desc, grid, stream)); }
+  else {
+    bz_tables tables = lens->tables;
+    if(lens->mode == BZ_MODE_LANES) { tables.packet_count = 0u; }
+    BZ_CUDA(bz_launch_warp_trace(job, tables, desc, grid, stream));
+  }
   BZ_CUDA(cudaEventRecord(lens->ev_end, stream));
   lens->last_stream = stream;
   lens->timed = true;

@@ -108,7 +108,8 @@ typedef struct bz_bezier bz_bezier;   /* host object: BezierMesh, reference/bezi
 
 /* intersect strategy of a lens handle */
 #define BZ_MODE_BRUTE   0u   /* every ray tests every patch, reference loop order (bezierMesh.cpp:211) */
-#define BZ_MODE_CULLED  1u   /* exact candidate-set-preserving packet cull, then the same stage A/B */
+#define BZ_MODE_CULLED  1u   /* exact candidate-set-preserving cull (warp-cooperative packet walk, per-lane walk for incoherent packets), then the same stage A/B */
+#define BZ_MODE_LANES   2u   /* as BZ_MODE_CULLED with the packet walk switched off: every ray walks the hierarchy on its own lane (test / comparison arm) */
 
 const char *bz_last_error(void);
 int  bz_device_count(int *out_count);

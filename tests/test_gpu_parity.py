@@ -24,14 +24,14 @@ def bz():
 
 
 @pytest.mark.parametrize("name", CONFIGS)
-@pytest.mark.parametrize("mode", ["brute", "culled"])
+@pytest.mark.parametrize("mode", ["brute", "culled", "lanes"])
 def test_intersect_batch_bit_exact(bz, oracle_built, name, mode):
     import bzoracle
     mesh, bezier, patches = common.ref_config(name)
     lo, hi = common.bbox(mesh)
     s, d = common.random_rays(lo, hi, 20000, seed=7)
     ref = bzoracle.intersect(patches, s, d, threads=8)
-    lens = bz.BezierLens(RI.get(name, 1.3), patches).set_mode(bz.MODE_BRUTE if mode == "brute" else bz.MODE_CULLED)
+    lens = bz.BezierLens(RI.get(name, 1.3), patches).set_mode({"brute": bz.MODE_BRUTE, "culled": bz.MODE_CULLED, "lanes": bz.MODE_LANES}[mode])
     got = lens.intersect(s, d)
     assert int((ref["what"] == 4).sum()) > 1000
     common.assert_same_hits(ref, got, "%s/%s" % (name, mode))
@@ -77,7 +77,8 @@ def test_refract_edge_cases(bz, oracle_built):
     assert list(gst) == [0, 0, 0]
 
 
-@pytest.mark.parametrize("name,w,h,strata,crossings", [("sphere16x8", 160, 120, 1, 2), ("sphere16x8", 64, 48, 4, 2), ("robot", 96, 64, 2, 8)])
+@pytest.mark.parametrize("name,w,h,strata,crossings", [("sphere16x8", 160, 120, 1, 2), ("sphere16x8", 64, 48, 4, 2), ("robot", 96, 64, 2, 8),
+                                                      ("sphere16x8", 131, 77, 3, 2), ("ellipsoid64x32", 67, 45, 1, 2)])   # ragged edge tiles, spp not a power of two
 def test_render_pixel_exact_vs_reference(bz, oracle_built, name, w, h, strata, crossings):
     import bzref
     mesh, bezier, patches = common.ref_config(name)
@@ -89,12 +90,16 @@ def test_render_pixel_exact_vs_reference(bz, oracle_built, name, w, h, strata, c
     rcam, rscene = bzref.make_camera(w, h, **cam_args), bzref.make_scene(bg_x=float(hi[0]) + 12.0, max_crossings=crossings)
     ref_rgba, ref_stats, rays = bzref.RefLens(ri, bezier).render(rcam, rscene, threads=8)
     cam, scene = bz.make_camera(w, h, **cam_args), bz.make_scene(bg_x=float(hi[0]) + 12.0, max_crossings=crossings)
-    for mode in (bz.MODE_CULLED, bz.MODE_BRUTE):
+    for mode in (bz.MODE_CULLED, bz.MODE_LANES, bz.MODE_BRUTE):
         rgba, stats = bz.BezierLens(ri, patches).set_mode(mode).render(cam, scene)
         assert np.array_equal(rgba, ref_rgba), "%d of %d pixels differ" % (int((rgba != ref_rgba).any(-1).sum()), w * h)
         got, want = stats.as_dict(), ref_stats.as_dict()
         for key in ("primary_rays", "refract_calls", "entered", "exited", "lost"):
             assert got[key] == want[key], key
+        if mode == bz.MODE_CULLED:      # camera rays go through the warp-cooperative walk (a coarse image of a fine mesh falls back in part)
+            assert stats.packet_walks > 0 and stats.lane_walk_calls < stats.refract_calls
+        if mode == bz.MODE_LANES:
+            assert stats.packet_walks == 0 and stats.lane_walk_calls == stats.refract_calls
     assert ref_stats.entered > 100
 
 
@@ -157,3 +162,29 @@ def test_queue_overflow_falls_back_inline(bz, oracle_built):
     ref = bzoracle.intersect(patches, s, d, threads=8)
     got = bz.BezierLens(1.3, patches).intersect(s, d)
     common.assert_same_hits(ref, got, "dense")
+
+
+def test_packet_walk_equals_lane_walk_on_coherent_batches(bz, oracle_built):
+    """parallel and fan-shaped ray grids (coherent packets: the warp-cooperative walk) against the per-lane walk and the oracle,
+    including rays that start inside the lens and a far origin beyond the hierarchy's origin limit"""
+    import bzoracle
+    mesh, bezier, patches = common.ref_config("ellipsoid64x32")
+    lo, hi = common.bbox(mesh)
+    ys, zs = np.meshgrid(np.linspace(lo[1] * 1.1, hi[1] * 1.1, 256, dtype=np.float32), np.linspace(lo[2] * 1.1, hi[2] * 1.1, 160, dtype=np.float32))
+    n = ys.size
+    cases = []
+    for x0 in (-10.0, 0.0, -2000.0):                                        # outside, inside the body, beyond origin_limit
+        s = np.stack([np.full(n, x0, np.float32), ys.ravel(), zs.ravel()], axis=1)
+        d = np.tile(np.array([[1, 0, 0]], np.float32), (n, 1))
+        cases.append((s, d))
+    eye = np.array([-9.0, 0.3, -0.2], np.float32)                            # a fan from one point
+    target = np.stack([np.zeros(n, np.float32), ys.ravel(), zs.ravel()], axis=1)
+    d = target - eye
+    d = (d / np.sqrt((d * d).sum(1, keepdims=True))).astype(np.float32)
+    cases.append((np.tile(eye, (n, 1)), d))
+    packet, lanes = bz.BezierLens(1.3, patches), bz.BezierLens(1.3, patches).set_mode(bz.MODE_LANES)
+    for s, d in cases:
+        ref = bzoracle.intersect(patches, s, d, threads=8)
+        common.assert_same_hits(ref, packet.intersect(s, d), "packet walk")
+        common.assert_same_hits(ref, lanes.intersect(s, d), "lane walk")
+    assert int((ref["what"] == 4).sum()) > 1000
