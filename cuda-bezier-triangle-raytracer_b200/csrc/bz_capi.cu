@@ -225,6 +225,16 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
       while(side > 2u && (uint64_t)side * side * spp > 1536u) { side /= 2u; }
       if(const char *env = std::getenv("BZ_B200_TILE")) { side = (uint32_t)std::max(2, std::atoi(env)); }     // tuning runs only (power of two)
       if((uint64_t)side * side * spp >= (1ull << 31)) { return bz_fail(BZ_ERR_INVALID, "too many samples per pixel"); }
+      // divisions by job constants become multiplications (exact while n * d < 2^32: n < tile_rays + 32 for spp,
+      // n < spp for strata, n < rows for stripe_rows)
+      auto reciprocal = [](uint32_t d, uint32_t out[2]) { out[0] = (d <= 1u) ? 0u : (uint32_t)(((1ull << 32) + d - 1u) / d); out[1] = (d == 1u) ? 1u : 0u; };
+      if(desc.camera.strata > 128u) { return bz_fail(BZ_ERR_INVALID, "more than 128 x 128 samples per pixel"); }
+      if((uint64_t)desc.rows * std::max(desc.stripe_rows, 1u) >= (1ull << 32)) { return bz_fail(BZ_ERR_INVALID, "band too large for the stripe layout"); }
+      reciprocal(spp, desc.div_spp);
+      reciprocal(desc.camera.strata, desc.div_strata);
+      reciprocal(desc.stripe_rows, desc.div_stripe);
+      desc.two_over_w = 2.0f / (float)desc.camera.width;
+      desc.two_over_h = 2.0f / (float)desc.camera.height;
       desc.tile_side = side;
       desc.tile_rays = side * side * spp;
       desc.tiles_x = (desc.camera.width + side - 1u) / side;

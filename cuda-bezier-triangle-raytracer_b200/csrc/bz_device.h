@@ -77,6 +77,8 @@ struct bz_job {
   // consecutive rays
   uint32_t  rows;            // RENDER: image rows of this call (local rows of the band)
   uint32_t  tile_side, tile_rays, tiles_x;
+  uint32_t  div_spp[2], div_strata[2], div_stripe[2];   // reciprocals for n / spp, n / strata, n / stripe_rows (bzw_div)
+  float     two_over_w, two_over_h;                      // 2.0f / (float)width, 2.0f / (float)height
   uint64_t  tile_count;
   unsigned long long *next_ray;   // tile counter, zeroed before launch
   unsigned long long *stats;      // 9 counters in bz_stats order, accumulated; nullable

@@ -118,12 +118,15 @@ __device__ __forceinline__ void bzw_load_newton_side(const float4 *p, bz_newton_
 }
 
 // K1: primary ray of sample (px, py, sx, sy); definitions in include/bz_capi.h (bz_camera).
-__device__ __forceinline__ void bzw_primary_ray(const bz_camera &cam, uint32_t px, uint32_t py, uint32_t sx, uint32_t sy, bzv3 &start, bzv3 &dir) {
+// two_over_w / two_over_h are the quotients 2.0f / (float)width and 2.0f / (float)height, formed once on the host (the same
+// IEEE division the per-ray code would do).
+__device__ __forceinline__ void bzw_primary_ray(const bz_camera &cam, float two_over_w, float two_over_h, uint32_t px, uint32_t py, uint32_t sx, uint32_t sy,
+                                                bzv3 &start, bzv3 &dir) {
   float strata = (float)cam.strata;
   float fu = (float)px + ((float)sx + 0.5f) / strata;
   float fv = (float)py + ((float)sy + 0.5f) / strata;
-  float a = (fu * (2.0f / (float)cam.width) - 1.0f) * cam.half_w;
-  float b = (1.0f - fv * (2.0f / (float)cam.height)) * cam.half_h;
+  float a = (fu * two_over_w - 1.0f) * cam.half_w;
+  float b = (1.0f - fv * two_over_h) * cam.half_h;
   bzv3 offset = bz_v(cam.right[0] * a + cam.up[0] * b, cam.right[1] * a + cam.up[1] * b, cam.right[2] * a + cam.up[2] * b);
   bzv3 raw;
   if(cam.ortho != 0u) {
@@ -192,7 +195,8 @@ __device__ __forceinline__ bzw_axis bzw_make_axis(float o_lo, float o_hi, float 
   // a vanishing slope is pushed to the permissive side (the lane walk treats |d| < 1e-20 the same way)
   if(fabsf(d_lo) < 1e-20f) { d_lo = -1e-20f; }
   if(fabsf(d_hi) < 1e-20f) { d_hi = 1e-20f; }
-  const float inv1 = 1.0f / d_lo, inv2 = 1.0f / d_hi;
+  // MUFU.RCP (<= 2 ulp): the error is of the size of the rounding the margin already covers
+  const float inv1 = __fdividef(1.0f, d_lo), inv2 = __fdividef(1.0f, d_hi);
   const float c1 = (margin - o_lo) * inv1;          // (1): t1 = hi * inv1 + c1
   const float c2 = (-margin - o_hi) * inv2;         // (2): t2 = lo * inv2 + c2
   bzw_axis a;
@@ -202,8 +206,12 @@ __device__ __forceinline__ bzw_axis bzw_make_axis(float o_lo, float o_hi, float 
   return a;
 }
 
-__device__ __forceinline__ void bzw_axis_bounds(const bzw_axis &a, const float *row, float &tnear, float &tfar) {
-  const float face_n = __ldg(row + a.off_n), face_f = __ldg(row + a.off_f);
+// `row` = this lane's entry in the axis's lo[] row of node 0; `node` = word offset of the node
+__device__ __forceinline__ void bzw_axis_bounds(const bzw_axis &a, const float *row, uint32_t node, float &tnear, float &tfar) {
+  // one pointer per packet and face, pinned in a register pair, so that a node costs one IMAD.WIDE per load
+  const float *near_face = row + a.off_n, *far_face = row + a.off_f;
+  asm volatile("" : "+l"(near_face), "+l"(far_face));
+  const float face_n = __ldg(near_face + node), face_f = __ldg(far_face + node);
   tnear = fmaxf(tnear, fmaxf(__fmaf_rn(face_n, a.in, a.cn), __fmaf_rn(face_f, a.ix, a.cx)));
   tfar = fminf(tfar, __fmaf_rn(face_f, a.jf, a.cf));
 }
@@ -225,6 +233,9 @@ __device__ __forceinline__ unsigned long long bzw_take_packet(unsigned long long
     while((uint32_t)(*(volatile unsigned long long*)cta_work >> 32) == tile) { __nanosleep(64); }
   }
 }
+
+// n / d for a per-job divisor d: div = { ceil(2^32 / d) mod 2^32, d == 1 }, exact while n * d < 2^32 (the host checks)
+__device__ __forceinline__ uint32_t bzw_div(uint32_t n, const uint32_t div[2]) { return __umulhi(n, div[0]) + n * div[1]; }
 
 // the even bits of v, compacted: x of a Morton index (y = bzw_even_bits(v >> 1))
 __device__ __forceinline__ uint32_t bzw_even_bits(uint32_t v) {
@@ -299,14 +310,16 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             bzv3 s, d;
             uint32_t expected = BZ_STATUS_INSIDE;
             if(JOB == BZ_JOB_RENDER) {
-              const uint32_t inside = at / spp, sample = at - inside * spp;              // pixel of the tile in Morton order, sample of the pixel
+              // (divisions by per-job constants are multiplications by the host's reciprocals, bz_job::div_*)
+              const uint32_t inside = bzw_div(at, J.div_spp), sample = at - inside * spp;   // pixel of the tile in Morton order, sample of the pixel
               const uint32_t tile_y = tile / J.tiles_x, tile_x = tile - tile_y * J.tiles_x;
               const uint32_t px = tile_x * J.tile_side + bzw_even_bits(inside), row = tile_y * J.tile_side + bzw_even_bits(inside >> 1);
               valid = valid && px < J.camera.width && row < J.rows;
               if(valid) {
+                const uint32_t stripe = bzw_div(row, J.div_stripe), sy = bzw_div(sample, J.div_strata);
                 const uint32_t py = (J.stripe_rows == 0u) ? J.row0 + row
-                                  : ((row / J.stripe_rows) * J.stripe_ranks + J.stripe_rank) * J.stripe_rows + row % J.stripe_rows;
-                bzw_primary_ray(J.camera, px, py, sample % J.camera.strata, sample / J.camera.strata, s, d);
+                                  : (stripe * J.stripe_ranks + J.stripe_rank) * J.stripe_rows + (row - stripe * J.stripe_rows);
+                bzw_primary_ray(J.camera, J.two_over_w, J.two_over_h, px, py, sample - sy * J.camera.strata, sy, s, d);
                 P.id_lo[slot] = row * J.camera.width + px;
               }
             }
@@ -367,12 +380,12 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             uint32_t visits = 0u;
             while(packet_done && sp != 0u) {
               --sp;
-              const float *box = T.packet + (size_t)P.stack[sp] * 224u + lane;
-              const uint32_t code = __float_as_uint(__ldg(box + 192));
+              const uint32_t node = P.stack[sp] * 224u;             // (the table has < 2^32 words: bz_lens_create checks)
+              const uint32_t code = __float_as_uint(__ldg(T.packet + lane + 192u + node));
               float tnear = 0.0f, tfar = inf;
-              bzw_axis_bounds(ax, box, tnear, tfar);
-              bzw_axis_bounds(ay, box + 32, tnear, tfar);
-              bzw_axis_bounds(az, box + 64, tnear, tfar);
+              bzw_axis_bounds(ax, T.packet + lane, node, tnear, tfar);
+              bzw_axis_bounds(ay, T.packet + lane + 32u, node, tnear, tfar);
+              bzw_axis_bounds(az, T.packet + lane + 64u, node, tnear, tfar);
               const bool hit = (code != 0u) && (tnear <= tfar);
               const bool inner = (code & 0x80000000u) != 0u;
               const uint32_t hit_inner = __ballot_sync(0xffffffffu, hit && inner);
