@@ -34,7 +34,7 @@
 #include "bz_math.cuh"
 
 #ifndef BZ_GROUPS
-#define BZ_GROUPS    1
+#define BZ_GROUPS    2
 #endif
 #ifndef BZ_WARPS
 #define BZ_WARPS     16      // one CTA per SM: its warps share tiles of the job (L1 locality), never a barrier
