@@ -196,7 +196,9 @@ __device__ __forceinline__ bzw_axis bzw_make_axis(float o_lo, float o_hi, float 
   if(fabsf(d_lo) < 1e-20f) { d_lo = -1e-20f; }
   if(fabsf(d_hi) < 1e-20f) { d_hi = 1e-20f; }
   // MUFU.RCP (<= 2 ulp): the error is of the size of the rounding the margin already covers
-  const float inv1 = __fdividef(1.0f, d_lo), inv2 = __fdividef(1.0f, d_hi);
+  float inv1, inv2;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv1) : "f"(d_lo));      // 1e-20 <= |d| <= 1: no range fix-up needed
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv2) : "f"(d_hi));
   const float c1 = (margin - o_lo) * inv1;          // (1): t1 = hi * inv1 + c1
   const float c2 = (-margin - o_hi) * inv2;         // (2): t2 = lo * inv2 + c2
   bzw_axis a;
