@@ -166,7 +166,18 @@ def main_ours(args, name):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # NCCL may print its version banner on stdout when the communicator is created: keep stdout for the ONE JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     assert world == args.gpus or world == 1, "--gpus must match the torchrun world size"
 
     # ---- setup (untimed): host preprocessing in the product's own C++ (bz::Mesh / bz::BezierMesh), tables to HBM ----
@@ -262,6 +273,14 @@ def main_ours(args, name):
                 peaks = json.load(f)
         except OSError:
             pass
+        traffic, traffic_source = None, None                   # DRAM bytes per launch of the same kernel from the committed ncu --set full capture
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                t = json.load(f)
+            if t.get("workload") == name and world == 1:
+                traffic, traffic_source = t["dram_bytes_read"] + t["dram_bytes_write"], t["source"]
+        except (OSError, KeyError, ValueError):
+            pass
         flop = FLOP_STAGE_A * own["stage_a"] + FLOP_STAGE_B * own["stage_b"] + FLOP_SNELL * own["snell"]     # rank 0's launch
         k_ms = float(kern.item())
         own_pixels = rows_local * width
@@ -269,8 +288,10 @@ def main_ours(args, name):
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         achieved_tf = flop / (k_ms * 1e-3) / 1e12
         roofline = {
-            "bound": "fp32_alu", "kernel": "bz_trace_kernel<RENDER, culled>", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-            "frac": achieved_tf / peak_tf, "traffic": None,
+            "bound": "fp32_alu", "kernel": "bz_warp_trace_kernel<RENDER> (packet walk)", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+            "frac": achieved_tf / peak_tf, "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_source,
+            "frac_of_no_fma_ceiling": achieved_tf / (peak_tf / 2.0),
+            "no_fma_note": "the parity build has no FMA contraction (bit-exact with the reference's x86 build): one flop per lane and instruction, half the probe's peak",
             "peak_source": "dependent-FMA probe kernel in this process (2 flop/lane/instr); nominal 148 SM x 128 lanes x 2 x %.0f MHz = %.1f"
                            % (peaks.get("sm_max_mhz", 1965.0), 148 * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12),
             "flop_model": "33 x stage_a + 1750 x stage_b + 45 x snell, executed counts (not brute-force-equivalent)",
