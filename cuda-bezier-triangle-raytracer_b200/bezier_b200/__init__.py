@@ -54,6 +54,41 @@ class Stats(C.Structure):
         return {n: int(getattr(self, n)) for n in STAT_NAMES}
 
 
+class Emitter(C.Structure):
+    """bz_emitter (include/bz_capi.h)"""
+    _fields_ = [("origin", C.c_float * 3), ("edge_u", C.c_float * 3), ("edge_v", C.c_float * 3), ("normal", C.c_float * 3),
+                ("tangent_a", C.c_float * 3), ("tangent_b", C.c_float * 3), ("points_u", C.c_uint32), ("points_v", C.c_uint32),
+                ("rays_per_point", C.c_uint32), ("belts", C.c_uint32), ("seed", C.c_uint64)]
+
+    @property
+    def rays(self):
+        return self.points_u * self.points_v * self.rays_per_point
+
+
+class Target(C.Structure):
+    """bz_target (include/bz_capi.h)"""
+    _fields_ = [("origin", C.c_float * 3), ("edge_u", C.c_float * 3), ("edge_v", C.c_float * 3), ("bins_u", C.c_uint32), ("bins_v", C.c_uint32)]
+
+
+LAND_LOST, LAND_MISSED = 0xffffffff, 0xfffffffe
+
+
+def make_emitter(origin, edge_u, edge_v, normal=(1.0, 0.0, 0.0), tangent_a=(0.0, 1.0, 0.0), tangent_b=(0.0, 0.0, 1.0),
+                 points=(4, 4), rays_per_point=1024, belts=16, seed=1):
+    em = Emitter()
+    em.origin[:], em.edge_u[:], em.edge_v[:] = origin, edge_u, edge_v
+    em.normal[:], em.tangent_a[:], em.tangent_b[:] = normal, tangent_a, tangent_b
+    em.points_u, em.points_v, em.rays_per_point, em.belts, em.seed = points[0], points[1], rays_per_point, belts, seed
+    return em
+
+
+def make_target(origin, edge_u, edge_v, bins=(64, 64)):
+    tg = Target()
+    tg.origin[:], tg.edge_u[:], tg.edge_v[:] = origin, edge_u, edge_v
+    tg.bins_u, tg.bins_v = bins
+    return tg
+
+
 def make_camera(width, height, strata=1, eye=(-12.0, 0.0, 0.0), half_w=0.5, half_h=None, ortho=False,
                 forward=(1.0, 0.0, 0.0), right=(0.0, 1.0, 0.0), up=(0.0, 0.0, 1.0)):
     cam = Camera()
@@ -131,6 +166,13 @@ SIGNATURES = {
     "bz_bezier_split_thick": (_int, [_vp, C.POINTER(_vp)]),
     "bz_lens_create_from_bezier": (_int, [_vp, _f, _int, C.POINTER(_vp)]),
     "bz_last_kernel_ms": (_int, [_vp, C.POINTER(_f)]),
+    "bz_sizeof_emitter": (_u32, []),
+    "bz_sizeof_target": (_u32, []),
+    "bz_hemisphere_patches": (_int, [_u32, C.POINTER(_u32), _vp, _vp]),
+    "bz_emit_rays": (_int, [C.POINTER(Emitter), _u64, _u64, _vp, _vp, _vp, _vp]),
+    "bz_trace_to_target": (_int, [_vp, _vp, _vp, _u64, C.POINTER(Target), _u32, _vp, _vp, _vp, _vp]),
+    "bz_illuminate": (_int, [_vp, C.POINTER(Emitter), C.POINTER(Target), _u32, _vp, _vp, _vp]),
+    "bz_illuminate_host": (_int, [_vp, C.POINTER(Emitter), C.POINTER(Target), _u32, _vp, C.POINTER(Stats)]),
 }
 
 
@@ -316,6 +358,28 @@ class BezierMesh:
         return Mesh(out)
 
 
+def hemisphere_patches(belts):
+    """UniformHemisphere belt table (reference/hostUtil.cpp:3-14) -> (patch count, width[belts], first[belts])"""
+    n = _u32(0)
+    width, first = np.zeros(belts, np.float32), np.zeros(belts, np.uint32)
+    _check(load().bz_hemisphere_patches(belts, C.byref(n), width.ctypes.data_as(_vp), first.ctypes.data_as(_vp)))
+    return n.value, width, first
+
+
+def emit_rays(emitter, first=0, count=None, device=0):
+    """bz_emit_rays on `device` -> host (start, dir, patch)"""
+    import torch
+    count = emitter.rays - first if count is None else count
+    dev = torch.device("cuda", device)
+    with torch.cuda.device(dev):
+        s = torch.zeros((count, 3), dtype=torch.float32, device=dev)
+        d = torch.zeros_like(s)
+        p = torch.zeros(count, dtype=torch.int32, device=dev)
+        _check(load().bz_emit_rays(C.byref(emitter), first, count, _ptr(s), _ptr(d), _ptr(p), _stream_handle(None)))
+        torch.cuda.synchronize()
+    return s.cpu().numpy(), d.cpu().numpy(), p.cpu().numpy().view(np.uint32)
+
+
 class BezierLens:
     """BezierLens(ri, bezier_mesh) -- reference/bezierLens.h:14-28.
 
@@ -387,6 +451,35 @@ class BezierLens:
         p = lambda a: a.ctypes.data_as(_vp)
         _check(self.lib.bz_intersect_batch_host(self.h, p(s), p(d), n, p(what), p(patch), p(dist), p(point), p(normal), p(cos), p(bary)))
         return dict(what=what, patch=patch, distance=dist, point=point, normal=normal, cos=cos, bary=bary)
+
+    def trace_to_target(self, start, direction, target, max_crossings=2):
+        """bz_trace_to_target over host rays -> (landing per ray, bins (bins_v, bins_u), Stats)"""
+        import torch
+        dev = torch.device("cuda", self.device)
+        with torch.cuda.device(dev):
+            s = torch.from_numpy(_np(start, np.float32, (-1, 3))).to(dev)
+            d = torch.from_numpy(_np(direction, np.float32, (-1, 3))).to(dev)
+            n = s.shape[0]
+            bins = torch.zeros((target.bins_v, target.bins_u), dtype=torch.int32, device=dev)
+            landing = torch.zeros(n, dtype=torch.int32, device=dev)
+            stats = torch.zeros(len(STAT_NAMES), dtype=torch.int64, device=dev)
+            _check(self.lib.bz_trace_to_target(self.h, _ptr(s), _ptr(d), n, C.byref(target), max_crossings, _ptr(bins), _ptr(landing), _ptr(stats),
+                                               _stream_handle(None)))
+            torch.cuda.synchronize()
+        out = Stats()
+        for name, value in zip(STAT_NAMES, stats.tolist()):
+            setattr(out, name, value)
+        return landing.cpu().numpy().view(np.uint32), bins.cpu().numpy().view(np.uint32), out
+
+    def illuminate(self, emitter, target, max_crossings=2, bins=None):
+        """bz_illuminate_host: the whole simulation -> (bins (bins_v, bins_u) uint32, Stats); `bins` is accumulated into when given"""
+        out = np.zeros((target.bins_v, target.bins_u), np.uint32) if bins is None else bins
+        stats = Stats()
+        _check(self.lib.bz_illuminate_host(self.h, C.byref(emitter), C.byref(target), max_crossings, out.ctypes.data_as(_vp), C.byref(stats)))
+        return out, stats
+
+    def illuminate_device(self, emitter, target, bins, max_crossings=2, stats=None, stream=None):
+        _check(self.lib.bz_illuminate(self.h, C.byref(emitter), C.byref(target), max_crossings, _ptr(bins), _ptr(stats), _stream_handle(stream)))
 
     def render(self, camera, scene, row0=0, row1=None):
         """host image of rows [row0,row1): (rows, width, 4) uint8, Stats"""

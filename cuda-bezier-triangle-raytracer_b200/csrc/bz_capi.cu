@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <algorithm>
 #include <cstdint>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -23,6 +24,10 @@ cudaError_t bz_launch_fma_probe(float *sink, uint32_t iters, int grid, cudaStrea
 int bz_trace_threads(void);
 cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream);
 cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta);
+cudaError_t bz_launch_emit(const bz_emitter &em, const bz_belts &belts, uint64_t first, uint64_t count, float *start, float *dir, uint32_t *patch,
+                           cudaStream_t stream);
+cudaError_t bz_launch_group_by_patch(const uint32_t *patch, uint64_t count, uint32_t patches, uint32_t *counts, const float *start, const float *dir,
+                                     float *out_start, float *out_dir, int sm_count, cudaStream_t stream);
 
 static thread_local std::string gError;
 
@@ -44,6 +49,8 @@ struct bz_lens {
   unsigned long long *d_counter;      // work counter of the persistent kernel
   uint32_t  *d_accum;                 // render scratch: one u32 per pixel of the largest band so far
   size_t     accum_pixels;
+  void      *d_illum;                 // illumination mode: emitted and grouped rays
+  size_t     illum_bytes;
   void      *d_scratch;               // *_host staging
   size_t     scratch_bytes;
   cudaEvent_t ev_begin, ev_end;
@@ -85,7 +92,7 @@ int bz_lens_destroy(bz_lens *lens) {
   if(lens == nullptr) { return BZ_OK; }
   cudaSetDevice(lens->device);
   cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_nodes); cudaFree(lens->d_packet);
-  cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch);
+  cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch); cudaFree(lens->d_illum);
   if(lens->ev_begin) { cudaEventDestroy(lens->ev_begin); }
   if(lens->ev_end) { cudaEventDestroy(lens->ev_end); }
   delete lens;
@@ -497,6 +504,146 @@ int bz_fp32_peak_probe(int device, float *out_tflops, float *out_ms) {
   double const flop = 2.0 * 8.0 * (double)iters * 256.0 * (double)grid;
   *out_tflops = (float)(flop / ((double)best * 1e-3) * 1e-12);
   if(out_ms != nullptr) { *out_ms = best; }
+  return BZ_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ illumination mode ----
+
+// UniformHemisphere::UniformHemisphere, reference/hostUtil.cpp:3-14: sin and ceil in double (the reference's ::sin(float) resolves
+// to the double overload), patch width and belt width in float
+static int bz_make_belts(uint32_t count, bz_belts &out) {
+  if(count == 0u || count > BZ_MAX_BELTS) { return bz_fail(BZ_ERR_INVALID, "belts must be 1..128"); }
+  const float pi = 3.14159265358979323846f;
+  std::memset(&out, 0, sizeof(out));
+  out.belts = count;
+  out.belt_width = pi / 2.0f / (float)count;
+  uint32_t total = 0u;
+  for(uint32_t i = 0u; i < count; ++i) {
+    float const angle = (2.0f * (float)i + 1.0f) / (4.0f * (float)count) * pi;
+    uint32_t const now = (uint32_t)std::ceil((double)(4.0f * (float)count) * std::sin((double)angle));
+    out.width[i] = pi * 2.0f / (float)now;
+    out.first[i] = total;
+    total += now;
+  }
+  out.patches = total;
+  return BZ_OK;
+}
+
+static int bz_check_emitter(const bz_emitter *em, uint64_t *out_rays) {
+  if(em == nullptr) { return bz_fail(BZ_ERR_INVALID, "emitter is null"); }
+  if(em->points_u == 0u || em->points_v == 0u || em->rays_per_point == 0u) { return bz_fail(BZ_ERR_INVALID, "empty emitter"); }
+  *out_rays = (uint64_t)em->points_u * em->points_v * em->rays_per_point;
+  return BZ_OK;
+}
+
+extern "C" {
+
+uint32_t bz_sizeof_emitter(void) { return (uint32_t)sizeof(bz_emitter); }
+uint32_t bz_sizeof_target(void) { return (uint32_t)sizeof(bz_target); }
+
+int bz_hemisphere_patches(uint32_t belts, uint32_t *out_patch_count, float *out_width, uint32_t *out_first) {
+  bz_belts table;
+  int rc = bz_make_belts(belts, table);
+  if(rc != BZ_OK) { return rc; }
+  if(out_patch_count != nullptr) { *out_patch_count = table.patches; }
+  for(uint32_t i = 0u; i < belts; ++i) {
+    if(out_width != nullptr) { out_width[i] = table.width[i]; }
+    if(out_first != nullptr) { out_first[i] = table.first[i]; }
+  }
+  return BZ_OK;
+}
+
+int bz_emit_rays(const bz_emitter *emitter, uint64_t first, uint64_t count, float *d_start, float *d_dir, uint32_t *d_patch, void *stream) {
+  uint64_t rays = 0u;
+  int rc = bz_check_emitter(emitter, &rays);
+  if(rc != BZ_OK) { return rc; }
+  if(first > rays || count > rays - first) { return bz_fail(BZ_ERR_INVALID, "ray range beyond the emission"); }
+  if(count != 0u && (d_start == nullptr || d_dir == nullptr)) { return bz_fail(BZ_ERR_INVALID, "null ray buffer"); }
+  bz_belts table;
+  rc = bz_make_belts(emitter->belts, table);
+  if(rc != BZ_OK) { return rc; }
+  int devices = 0;
+  if(cudaGetDeviceCount(&devices) != cudaSuccess || devices == 0) { cudaGetLastError(); return bz_fail(BZ_ERR_NO_DEVICE, "no usable CUDA device (there is no CPU path)"); }
+  BZ_CUDA(bz_launch_emit(*emitter, table, first, count, d_start, d_dir, d_patch, (cudaStream_t)stream));
+  return BZ_OK;
+}
+
+int bz_trace_to_target(bz_lens *lens, const float *d_start, const float *d_dir, uint64_t n, const bz_target *target, uint32_t max_crossings,
+                       uint32_t *d_bins, uint32_t *d_landing, bz_stats *d_stats, void *stream) {
+  if(lens == nullptr || target == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  if(target->bins_u == 0u || target->bins_v == 0u || (uint64_t)target->bins_u * target->bins_v >= BZ_LAND_MISSED) { return bz_fail(BZ_ERR_INVALID, "bad bin counts"); }
+  if(n != 0u && (d_start == nullptr || d_dir == nullptr || d_bins == nullptr)) { return bz_fail(BZ_ERR_INVALID, "null buffer"); }
+  if(lens->mode == BZ_MODE_BRUTE) { return bz_fail(BZ_ERR_INVALID, "the illumination mode runs on the culled kernel only"); }
+  bz_job desc;
+  std::memset(&desc, 0, sizeof(desc));
+  desc.in_start = d_start; desc.in_dir = d_dir;
+  desc.target = *target;
+  // plane of the rectangle: unit normal of edge_u x edge_v (normalised like Eigen's normalized()), constant = n . origin
+  const float *u = target->edge_u, *v = target->edge_v;
+  float const cx = u[1] * v[2] - u[2] * v[1], cy = u[2] * v[0] - u[0] * v[2], cz = u[0] * v[1] - u[1] * v[0];
+  float const length = std::sqrt(cx * cx + (cy * cy + cz * cz));
+  if(!(length > 0.0f)) { return bz_fail(BZ_ERR_INVALID, "degenerate target rectangle"); }
+  desc.target_plane[0] = cx / length; desc.target_plane[1] = cy / length; desc.target_plane[2] = cz / length;
+  desc.target_plane[3] = desc.target_plane[0] * target->origin[0] + (desc.target_plane[1] * target->origin[1] + desc.target_plane[2] * target->origin[2]);
+  desc.bins = d_bins;
+  desc.out_landing = d_landing;
+  desc.scene.max_crossings = max_crossings;
+  desc.ray_count = n;
+  desc.stats = (unsigned long long*)d_stats;
+  return bz_run(lens, BZ_JOB_TARGET, desc, (cudaStream_t)stream);
+}
+
+int bz_illuminate(bz_lens *lens, const bz_emitter *emitter, const bz_target *target, uint32_t max_crossings,
+                  uint32_t *d_bins, bz_stats *d_stats, void *stream) {
+  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+  uint64_t rays = 0u;
+  int rc = bz_check_emitter(emitter, &rays);
+  if(rc != BZ_OK) { return rc; }
+  bz_belts table;
+  rc = bz_make_belts(emitter->belts, table);
+  if(rc != BZ_OK) { return rc; }
+  BZ_CUDA(cudaSetDevice(lens->device));
+  // scratch of the lens handle: emitted rays, patch keys, group offsets, grouped rays
+  size_t const keys = ((size_t)rays * 4u + 255u) / 256u * 256u, counts = ((size_t)table.patches * 4u + 255u) / 256u * 256u;
+  if(lens->d_illum == nullptr || lens->illum_bytes < (size_t)rays * 48u + keys + counts) {
+    if(lens->d_illum != nullptr) { BZ_CUDA(cudaFree(lens->d_illum)); lens->d_illum = nullptr; lens->illum_bytes = 0u; }
+    BZ_CUDA(cudaMalloc(&lens->d_illum, (size_t)rays * 48u + keys + counts));
+    lens->illum_bytes = (size_t)rays * 48u + keys + counts;
+  }
+  cudaStream_t const st = (cudaStream_t)stream;
+  float *start = (float*)lens->d_illum, *dir = start + rays * 3u, *sorted_start = dir + rays * 3u, *sorted_dir = sorted_start + rays * 3u;
+  uint32_t *patch = (uint32_t*)(sorted_dir + rays * 3u), *group = (uint32_t*)((char*)patch + keys);
+  BZ_CUDA(bz_launch_emit(*emitter, table, 0u, rays, start, dir, patch, st));
+  BZ_CUDA(cudaMemsetAsync(group, 0, counts, st));
+  BZ_CUDA(bz_launch_group_by_patch(patch, rays, table.patches, group, start, dir, sorted_start, sorted_dir, lens->sm_count, st));
+  return bz_trace_to_target(lens, sorted_start, sorted_dir, rays, target, max_crossings, d_bins, nullptr, d_stats, stream);
+}
+
+int bz_illuminate_host(bz_lens *lens, const bz_emitter *emitter, const bz_target *target, uint32_t max_crossings,
+                       uint32_t *h_bins, bz_stats *h_stats) {
+  if(lens == nullptr || target == nullptr || h_bins == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  size_t const bytes = (size_t)target->bins_u * target->bins_v * 4u;
+  if(bytes == 0u) { return bz_fail(BZ_ERR_INVALID, "bad bin counts"); }
+  int rc = bz_scratch(lens, bytes + 128u);
+  if(rc != BZ_OK) { return rc; }
+  bz_stats *d_stats = (bz_stats*)lens->d_scratch;
+  uint32_t *d_bins = (uint32_t*)((uint8_t*)lens->d_scratch + 128u);
+  BZ_CUDA(cudaMemsetAsync(d_stats, 0, sizeof(bz_stats), 0));
+  BZ_CUDA(cudaMemcpyAsync(d_bins, h_bins, bytes, cudaMemcpyHostToDevice, 0));      // accumulate into the caller's counts
+  rc = bz_illuminate(lens, emitter, target, max_crossings, d_bins, h_stats != nullptr ? d_stats : nullptr, nullptr);
+  if(rc != BZ_OK) { return rc; }
+  BZ_CUDA(cudaMemcpyAsync(h_bins, d_bins, bytes, cudaMemcpyDeviceToHost, 0));
+  if(h_stats != nullptr) {
+    bz_stats fresh;
+    BZ_CUDA(cudaMemcpyAsync(&fresh, d_stats, sizeof(bz_stats), cudaMemcpyDeviceToHost, 0));
+    BZ_CUDA(cudaStreamSynchronize(0));
+    uint64_t *acc = (uint64_t*)h_stats;
+    const uint64_t *add = (const uint64_t*)&fresh;
+    for(size_t i = 0u; i < sizeof(bz_stats) / sizeof(uint64_t); ++i) { acc[i] += add[i]; }
+  }
+  BZ_CUDA(cudaStreamSynchronize(0));
   return BZ_OK;
 }
 

@@ -47,6 +47,7 @@ struct bz_tables {
 #define BZ_JOB_RENDER     0
 #define BZ_JOB_REFRACT    1
 #define BZ_JOB_INTERSECT  2
+#define BZ_JOB_TARGET     3     // bounce loop over a ray batch, then the target rectangle of the illumination mode
 
 struct bz_job {
   // BZ_JOB_RENDER
@@ -70,6 +71,11 @@ struct bz_job {
   float    *out_normal;
   float    *out_cos;
   float    *out_bary;
+  // BZ_JOB_TARGET (rays from in_start / in_dir, bounce limit from scene.max_crossings)
+  bz_target target;
+  float     target_plane[4];   // unit normal of the target rectangle and its constant
+  uint32_t *bins;              // bins_v x bins_u counters, accumulated
+  uint32_t *out_landing;       // nullable: per ray the bin, BZ_LAND_LOST or BZ_LAND_MISSED
   // all
   uint64_t  ray_count;       // primary rays of this call
   // work distribution: the job is cut into tiles handed to CTAs; RENDER: square blocks of tile_side x tile_side pixels
@@ -82,6 +88,15 @@ struct bz_job {
   uint64_t  tile_count;
   unsigned long long *next_ray;   // tile counter, zeroed before launch
   unsigned long long *stats;      // 9 counters in bz_stats order, accumulated; nullable
+};
+
+// UniformHemisphere belt table (reference/hostUtil.cpp:8-13), passed to the emission kernel by value
+#define BZ_MAX_BELTS 128
+struct bz_belts {
+  float    width[BZ_MAX_BELTS];     // patch width of the belt: 2 pi / patches of the belt
+  uint32_t first[BZ_MAX_BELTS];     // patches before the belt
+  float    belt_width;              // pi / 2 / belts
+  uint32_t belts, patches;
 };
 
 #endif

@@ -162,6 +162,25 @@ __device__ __forceinline__ uint32_t bzw_shade_background(const bz_scene &sc, con
   return (pa != pb) ? sc.value_bright : sc.value_dark;
 }
 
+// Illumination mode: where a ray in air lands on the target rectangle (include/bz_capi.h, bz_target): the bin index,
+// or BZ_LAND_MISSED.  Plane::intersect semantics (3dGeomUtil.h:279-296).
+__device__ __forceinline__ uint32_t bzw_land_on_target(const bz_job &J, const bzv3 &start, const bzv3 &dir) {
+  const bzv3 n = bz_v(J.target_plane[0], J.target_plane[1], J.target_plane[2]);
+  const float cosine = bz_dot(dir, n);
+  if(!(fabsf(cosine) >= BZ_PLANE_EPSILON)) { return BZ_LAND_MISSED; }
+  const float distance = (J.target_plane[3] - bz_dot(n, start)) / cosine;
+  if(!(distance > 0.0f)) { return BZ_LAND_MISSED; }
+  const bzv3 rel = bz_v(start.x + distance * dir.x - J.target.origin[0], start.y + distance * dir.y - J.target.origin[1],
+                        start.z + distance * dir.z - J.target.origin[2]);
+  const bzv3 eu = bz_v(J.target.edge_u[0], J.target.edge_u[1], J.target.edge_u[2]);
+  const bzv3 ev = bz_v(J.target.edge_v[0], J.target.edge_v[1], J.target.edge_v[2]);
+  const float su = bz_dot(rel, eu) / bz_dot(eu, eu), sv = bz_dot(rel, ev) / bz_dot(ev, ev);
+  if(!(su >= 0.0f && su < 1.0f && sv >= 0.0f && sv < 1.0f)) { return BZ_LAND_MISSED; }
+  const uint32_t bu = min((uint32_t)(su * (float)J.target.bins_u), J.target.bins_u - 1u);
+  const uint32_t bv = min((uint32_t)(sv * (float)J.target.bins_v), J.target.bins_v - 1u);
+  return bv * J.target.bins_u + bu;
+}
+
 __device__ __forceinline__ unsigned long long bzw_make_key(float distance, uint32_t loop_index) {
   return ((unsigned long long)bz_float_key(distance) << 32) | (unsigned long long)loop_index;
 }
@@ -331,7 +350,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
               if(valid) {
                 s = bz_v(J.in_start[id * 3u], J.in_start[id * 3u + 1u], J.in_start[id * 3u + 2u]);
                 d = bz_v(J.in_dir[id * 3u], J.in_dir[id * 3u + 1u], J.in_dir[id * 3u + 2u]);
-                expected = (JOB == BZ_JOB_REFRACT) ? (J.in_expected[id] & 3u) : 0u;
+                expected = (JOB == BZ_JOB_REFRACT) ? (J.in_expected[id] & 3u) : ((JOB == BZ_JOB_TARGET) ? BZ_STATUS_INSIDE : 0u);
                 P.id_lo[slot] = (uint32_t)id;
                 P.id_hi[slot] = (uint32_t)(id >> 32);
               }
@@ -692,14 +711,20 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           }
           if(done) {
             uint32_t value;
-            if(expected == BZ_STATUS_INSIDE) {      // the ray is in air: it reaches the background
-              value = bzw_shade_background(J.scene, s, d);
+            if(expected == BZ_STATUS_INSIDE) {      // the ray is in air: it reaches the background (RENDER) / the target (TARGET)
+              value = (JOB == BZ_JOB_TARGET) ? bzw_land_on_target(J, s, d) : bzw_shade_background(J.scene, s, d);
             }
             else {                                  // entered and never left
-              value = J.scene.value_lost;
+              value = (JOB == BZ_JOB_TARGET) ? BZ_LAND_LOST : J.scene.value_lost;
               events |= 8u;
             }
-            atomicAdd(J.accum + P.id_lo[slot], value);
+            if(JOB == BZ_JOB_TARGET) {
+              if(value < BZ_LAND_MISSED) { atomicAdd(J.bins + value, 1u); }
+              if(J.out_landing != nullptr) { J.out_landing[((unsigned long long)P.id_hi[slot] << 32) | P.id_lo[slot]] = value; }
+            }
+            else {
+              atomicAdd(J.accum + P.id_lo[slot], value);
+            }
             live = false;
           }
           else {
@@ -736,6 +761,7 @@ static cudaError_t bzw_configure() {
   e = cudaFuncSetAttribute(bz_warp_trace_kernel<BZ_JOB_RENDER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bzw_shared_bytes());
   if(e == cudaSuccess) { e = cudaFuncSetAttribute(bz_warp_trace_kernel<BZ_JOB_REFRACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bzw_shared_bytes()); }
   if(e == cudaSuccess) { e = cudaFuncSetAttribute(bz_warp_trace_kernel<BZ_JOB_INTERSECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bzw_shared_bytes()); }
+  if(e == cudaSuccess) { e = cudaFuncSetAttribute(bz_warp_trace_kernel<BZ_JOB_TARGET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bzw_shared_bytes()); }
   configured = (e == cudaSuccess);
   return e;
 }
@@ -745,6 +771,7 @@ cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job 
   if(e != cudaSuccess) { return e; }
   if(job == BZ_JOB_RENDER) { bz_warp_trace_kernel<BZ_JOB_RENDER><<<grid, 32 * BZ_WARPS, bzw_shared_bytes(), stream>>>(tables, desc); }
   else if(job == BZ_JOB_REFRACT) { bz_warp_trace_kernel<BZ_JOB_REFRACT><<<grid, 32 * BZ_WARPS, bzw_shared_bytes(), stream>>>(tables, desc); }
+  else if(job == BZ_JOB_TARGET) { bz_warp_trace_kernel<BZ_JOB_TARGET><<<grid, 32 * BZ_WARPS, bzw_shared_bytes(), stream>>>(tables, desc); }
   else { bz_warp_trace_kernel<BZ_JOB_INTERSECT><<<grid, 32 * BZ_WARPS, bzw_shared_bytes(), stream>>>(tables, desc); }
   return cudaGetLastError();
 }

@@ -204,6 +204,61 @@ int  bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *s
 int  bz_assemble_stripes(const uint8_t *d_bands, uint32_t band_rows, uint32_t width, uint32_t height, uint32_t stripe_rows,
                          uint32_t ranks, uint8_t *d_rgba, void *stream);
 
+/* ---- illumination mode (reference/hostUtil.h:8-28, hostUtil.cpp:3-29, README.md:161-194) ----
+ * A rectangular emitter behind the lens casts rays into the hemisphere around its normal; the rays cross the lens
+ * (the same bounce loop as the renderer) and are counted where they land on a rectangular target.
+ *
+ * UniformHemisphere (hostUtil.cpp:3-29): belt i of `belts` has ceil(4 b sin((2i+1)/(4b) pi)) patches (double sin, as the
+ * reference's ::sin resolves); a draw is incidence = acos(u1), turn = u2 * 2pi, direction (cos inc, sin inc cos turn,
+ * sin inc sin turn) normalised, patch = first[belt] + turn / patch_width[belt], belt = incidence / (pi / 2 / belts).
+ * The reference draws u1, u2 from std::ranlux24_base; here they come from a counter-based generator (statistical, not
+ * bit, parity with the reference's stream): u = (splitmix64(seed + (2 * ray + draw) * 0x9E3779B97F4A7C15) >> 40) * 2^-24.
+ * Emission order: ray = (point_v * points_u + point_u) * rays_per_point + k; the point is the centre of its grid cell. */
+typedef struct bz_emitter {
+  float    origin[3];        /* corner of the emitter rectangle */
+  float    edge_u[3];        /* its two edges */
+  float    edge_v[3];
+  float    normal[3];        /* unit axis of the hemisphere (direction(0) of hostUtil.cpp:22) */
+  float    tangent_a[3];     /* unit, direction(1) */
+  float    tangent_b[3];     /* unit, direction(2) */
+  uint32_t points_u, points_v;
+  uint32_t rays_per_point;
+  uint32_t belts;
+  uint64_t seed;
+} bz_emitter;
+
+/* Target rectangle origin + s*edge_u + t*edge_v (edges orthogonal), bins_u x bins_v counting bins, row-major in v.
+ * A ray in air meets the plane with Plane::intersect semantics (3dGeomUtil.h:279-296); s = ((P-origin).edge_u)/(edge_u.edge_u),
+ * likewise t; it counts for bin (floor(t*bins_v), floor(s*bins_u)) when 0 <= s,t < 1. */
+typedef struct bz_target {
+  float    origin[3];
+  float    edge_u[3];
+  float    edge_v[3];
+  uint32_t bins_u, bins_v;
+} bz_target;
+
+#define BZ_LAND_LOST    0xffffffffu   /* the ray entered the lens and never left (or was still inside after max_crossings) */
+#define BZ_LAND_MISSED  0xfffffffeu   /* the ray ended in air but does not meet the target rectangle */
+
+uint32_t bz_sizeof_emitter(void);
+uint32_t bz_sizeof_target(void);
+/* UniformHemisphere::getPatchCount and the belt table (hostUtil.cpp:8-13): out_width / out_first hold `belts` entries (nullable) */
+int  bz_hemisphere_patches(uint32_t belts, uint32_t *out_patch_count, float *out_width, uint32_t *out_first);
+/* UniformHemisphere::getRandom for rays [first, first + count) of the emission order: start, direction (n x 3 floats) and
+ * hemisphere patch index per ray (d_patch nullable). */
+int  bz_emit_rays(const bz_emitter *emitter, uint64_t first, uint64_t count, float *d_start, float *d_dir, uint32_t *d_patch, void *stream);
+/* Bounce loop (as bz_render: expected = inside first, at most max_crossings refract() calls) over a ray batch, then the target:
+ * d_bins (bins_v x bins_u u32) is ACCUMULATED into; d_landing (nullable) gets the bin index, BZ_LAND_LOST or BZ_LAND_MISSED
+ * per ray.  d_stats as bz_render. */
+int  bz_trace_to_target(bz_lens *lens, const float *d_start, const float *d_dir, uint64_t n, const bz_target *target, uint32_t max_crossings,
+                        uint32_t *d_bins, uint32_t *d_landing, bz_stats *d_stats, void *stream);
+/* The whole simulation: emit -> group the rays by hemisphere patch (counting sort: rays of one patch have similar directions,
+ * README.md:176-186) -> bz_trace_to_target.  d_bins is accumulated into. */
+int  bz_illuminate(bz_lens *lens, const bz_emitter *emitter, const bz_target *target, uint32_t max_crossings,
+                   uint32_t *d_bins, bz_stats *d_stats, void *stream);
+int  bz_illuminate_host(bz_lens *lens, const bz_emitter *emitter, const bz_target *target, uint32_t max_crossings,
+                        uint32_t *h_bins, bz_stats *h_stats);
+
 /* Cull-hierarchy facts of a lens: out[0] = 4-wide nodes, out[1] = levels, out[2] = patches in the
  * always-tested segment, out[3] = SM count of the device. */
 int  bz_lens_info(const bz_lens *lens, uint32_t out[4]);

@@ -36,6 +36,12 @@ def load():
     lib.bzo_patch_intersect.argtypes = [vp, fp, fp, u32, fp, fp, fp, fp, fp]
     lib.bzo_interpolate.restype = None
     lib.bzo_interpolate.argtypes = [vp, f, f, f, fp]
+    lib.bzo_hemisphere.restype = u32
+    lib.bzo_hemisphere.argtypes = [u32, fp, up]
+    lib.bzo_emit.restype = None
+    lib.bzo_emit.argtypes = [vp, u64, u64, fp, fp, up]
+    lib.bzo_land.restype = None
+    lib.bzo_land.argtypes = [vp, fp, fp, C.POINTER(C.c_uint8), u64, up, up]
     _lib = lib
     return lib
 
@@ -105,3 +111,51 @@ def interpolate(patches, index, b0, b1, b2):
     out = np.zeros(3, np.float32)
     lib.bzo_interpolate(patches.ctypes.data + 256 * int(index), b0, b1, b2, _fp(out))
     return out
+
+
+# ---- illumination mode (oracle/bz_oracle_illum.c); emitter / target are the ctypes structures of the product binding or
+# any object with the same memory layout (include/bz_capi.h: bz_emitter, bz_target) ----
+LAND_LOST, LAND_MISSED = 0xffffffff, 0xfffffffe
+
+
+def hemisphere(belts):
+    """UniformHemisphere belt table -> (patch count, width[belts], first[belts])"""
+    lib = load()
+    width, first = np.zeros(belts, np.float32), np.zeros(belts, np.uint32)
+    return int(lib.bzo_hemisphere(belts, _fp(width), _up(first))), width, first
+
+
+def emit(emitter, first, count):
+    """UniformHemisphere::getRandom with the C ABI's counter-based generator -> (start, dir, patch)"""
+    lib = load()
+    s, d, p = np.zeros((count, 3), np.float32), np.zeros((count, 3), np.float32), np.zeros(count, np.uint32)
+    lib.bzo_emit(C.addressof(emitter), first, count, _fp(s), _fp(d), _up(p))
+    return s, d, p
+
+
+def trace_to_target(patches, ri, start, direction, target, max_crossings, threads=1):
+    """bounce loop of bz_render / bz_trace_to_target around refract(), then the landing on the target -> (landing, bins, counts)"""
+    lib = load()
+    s, d = _f32(start, (-1, 3)).copy(), _f32(direction, (-1, 3)).copy()
+    n = s.shape[0]
+    expected = np.full(n, 1, np.uint32)
+    alive = np.ones(n, bool)
+    counts = dict(refract_calls=0, entered=0, exited=0)
+    for _ in range(max_crossings):
+        idx = np.nonzero(alive)[0]
+        if idx.size == 0:
+            break
+        os_, od, st, _, _ = refract(patches, ri, s[idx], d[idx], expected[idx], threads)
+        counts["refract_calls"] += int(idx.size)
+        counts["entered"] += int((st == 1).sum())
+        counts["exited"] += int((st == 2).sum())
+        ok = st != 0
+        s[idx[ok]], d[idx[ok]] = os_[ok], od[ok]
+        expected[idx[ok]] = 3 - expected[idx[ok]]
+        alive[idx[~ok]] = False
+    in_air = np.ascontiguousarray((expected == 1).astype(np.uint8))
+    landing = np.zeros(n, np.uint32)
+    bins = np.zeros(target.bins_v * target.bins_u, np.uint32)
+    lib.bzo_land(C.addressof(target), _fp(s), _fp(d), in_air.ctypes.data_as(C.POINTER(C.c_uint8)), n, _up(landing), _up(bins))
+    counts["lost"] = int((landing == LAND_LOST).sum())
+    return landing, bins.reshape(target.bins_v, target.bins_u), counts
