@@ -97,6 +97,11 @@ public:
     check(bz_render_host(mLens, &aCamera, &aScene, aRow0, aRow1, aRgba, aStats));
   }
 
+  // illumination mode (README.md:161-194): emitter -> lens -> counting bins of a target rectangle, host bins are accumulated into
+  void illuminate(bz_emitter const &aEmitter, bz_target const &aTarget, uint32_t const aMaxCrossings, uint32_t *aBins, bz_stats *aStats = nullptr) const {
+    check(bz_illuminate_host(mLens, &aEmitter, &aTarget, aMaxCrossings, aBins, aStats));
+  }
+
   float getRefractiveIndex() const { return mRefractiveIndex; }
   uint32_t size() const { return mPatchCount; }
   bz_lens *handle() const { return mLens; }       // for the device-pointer entry points of the C ABI

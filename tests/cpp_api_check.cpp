@@ -6,6 +6,7 @@
 #include <cstring>
 #include <stdexcept>
 #include "bz_bezier_lens.h"
+#include "bz_hemisphere.h"
 
 int main(int argc, char **argv) {
   bool const gpu = (argc > 1 && std::strcmp(argv[1], "gpu") == 0);
@@ -35,6 +36,11 @@ int main(int argc, char **argv) {
     return 1;
   }
   catch(char const *text) { if(std::strcmp(text, "Vertex on edge detected.") != 0) { return 1; } }   // mesh.cpp:204
+  bz::UniformHemisphere hemisphere(16u);                             // host part of the emitter sampler (hostUtil.cpp:3-14)
+  if(hemisphere.getPatchCount() != 660u || hemisphere.getBelt(0u).second != 0u || hemisphere.getBelt(1u).second != 4u) {
+    std::printf("bad hemisphere %u\n", hemisphere.getPatchCount());
+    return 1;
+  }
   try {
     bz::BezierLens lens(1.3f, bezier);
     if(!gpu) { std::printf("lens built without a device?\n"); return 1; }
@@ -47,6 +53,16 @@ int main(int argc, char **argv) {
     if(out.second != bz::RefractionResult::cOutside || std::fabs(out.first.mDirection.x - 0.99463236f) > 2e-6f) { std::printf("bad exit\n"); return 1; }
     auto const wrong = lens.refract(ray, bz::RefractionResult::cOutside);
     if(wrong.second != bz::RefractionResult::cNone) { std::printf("expected-side check failed\n"); return 1; }
+    // illumination mode: a small emitter in front of the sphere, a target behind it
+    bz_emitter emitter = { {-3.0f, -0.1f, -0.1f}, {0.0f, 0.2f, 0.0f}, {0.0f, 0.0f, 0.2f}, {1.0f, 0.0f, 0.0f}, {0.0f, 1.0f, 0.0f}, {0.0f, 0.0f, 1.0f},
+                           2u, 2u, 2048u, 16u, 7u };
+    bz_target target = { {4.0f, -2.0f, -2.0f}, {0.0f, 4.0f, 0.0f}, {0.0f, 0.0f, 4.0f}, 8u, 8u };
+    uint32_t bins[64] = {};
+    bz_stats stats = {};
+    lens.illuminate(emitter, target, 2u, bins, &stats);
+    uint64_t landed = 0u;
+    for(uint32_t b : bins) { landed += b; }
+    if(stats.primary_rays != 8192u || stats.entered == 0u || landed == 0u || landed > 8192u) { std::printf("bad illumination %llu\n", (unsigned long long)landed); return 1; }
     std::printf("ok gpu\n");
   }
   catch(std::runtime_error const &e) {
