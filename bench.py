@@ -328,10 +328,69 @@ def main_ours(args, name):
         dist.destroy_process_group()
 
 
+def main_illumination(args, name):
+    """secondary workload: the illumination mode (emit -> group by hemisphere patch -> bounce loop -> target bins), 1 GPU"""
+    import torch
+    import bezier_b200 as bz
+    from bezier_b200 import workloads
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    if not torch.cuda.is_available() or bz.device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path")
+    spec, mesh, em_kw, tg_kw = workloads.setup_illumination(name, bz.Mesh)
+    lens = bz.BezierLens(spec["ri"], bz.BezierMesh(mesh), device=0)
+    emitter, target = bz.make_emitter(**em_kw), bz.make_target(**tg_kw)
+    dev = torch.device("cuda", 0)
+    bins = torch.zeros((target.bins_v, target.bins_u), dtype=torch.int32, device=dev)
+    stats = torch.zeros(len(bz.STAT_NAMES), dtype=torch.int64, device=dev)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+    def step():
+        flush.fill_(1)
+        bins.zero_()
+        lens.illuminate_device(emitter, target, bins, spec["max_crossings"], stats=stats)
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    stats.zero_()
+    sampler = ClockSampler(0)
+    begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    wall0 = time.time()
+    begin.record()
+    for _ in range(args.steps):
+        step()
+    end.record()
+    torch.cuda.synchronize()
+    wall1 = time.time()
+    ms = begin.elapsed_time(end) / args.steps
+    clocks = sampler.stop(wall0, wall1)
+    work = dict(zip(bz.STAT_NAMES, [int(x) // args.steps for x in stats.tolist()]))
+    host_bins = torch.zeros((target.bins_v, target.bins_u), dtype=torch.int32).pin_memory().numpy().view("uint32")
+    t0 = time.perf_counter()
+    for _ in range(3):
+        host_bins[:] = 0
+        lens.illuminate(emitter, target, spec["max_crossings"], bins=host_bins)          # C ABI: bz_illuminate_host
+    e2e_s = (time.perf_counter() - t0) / 3
+    rays = emitter.rays
+    print(json.dumps({
+        "metric": "Mrays/s", "value": rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 in the emitter's acos/sin/cos, as the reference)", "data": "synthetic",
+        "config": {"workload": name, "patches": lens.patch_count, "emitted_rays_per_step": rays, "belts": emitter.belts, "bins": "%dx%d" % (target.bins_u, target.bins_v),
+                   "max_crossings": spec["max_crossings"], "l2": "flushed between steps (256 MiB fill)"},
+        "e2e": {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(host_bins.nbytes + 140), "d2h_bytes_per_step": int(host_bins.nbytes),
+                "ms_per_step": e2e_s * 1e3, "call": "bz_illuminate_host"},
+        "gpu_launches": 6 * args.steps, "clocks": clocks, "work_per_step": work, "landed": int(bins.sum().item()),
+    }))
+
+
 def main():
     args = parse_args()
     from bezier_b200 import workloads
     name = args.workload or workloads.HEADLINE
+    if name in workloads.ILLUMINATION:
+        main_illumination(args, name)
+        return
     if args.impl == "reference":
         args.cpu_seconds = min(args.cpu_seconds, 150.0 / max(args.steps + args.warmup, 1))
         main_reference(args, name)

@@ -21,6 +21,11 @@ WORKLOADS = {
     "cfg4_freeform181x91_4k_16spp": dict(mesh=("ellipsoid", 181, 91, (1.0, 4.0, 2.0)), width=3840, height=2160, strata=4, ri=1.3, max_crossings=2),
 }
 WORKLOADS["cfg5_freeform181x91_4k_16spp_sharded"] = WORKLOADS["cfg4_freeform181x91_4k_16spp"]
+# illumination mode: an LED-sized emitter 1.5 lens depths in front of the lens, a target behind it
+ILLUMINATION = {
+    "illum_ellipsoid64x32_4m": dict(mesh=("ellipsoid", 64, 32, (1.0, 4.0, 2.0)), points=(8, 8), rays_per_point=65536, belts=16, bins=(256, 128),
+                                    ri=1.3, max_crossings=2),
+}
 HEADLINE = "cfg4_freeform181x91_4k_16spp"
 STRIPE_ROWS = 16
 
@@ -62,3 +67,19 @@ def setup(name, mesh_class):
     tri = mesh.triangles().reshape(-1, 3)
     camera, scene = frame(tri.min(0), tri.max(0), spec["width"], spec["height"], spec["strata"], spec["max_crossings"])
     return spec, mesh, camera, scene
+
+
+def setup_illumination(name, mesh_class):
+    """-> (spec, mesh, emitter kwargs, target kwargs) for bezier_b200.make_emitter / make_target"""
+    spec = ILLUMINATION[name]
+    mesh = build_mesh(mesh_class, spec["mesh"])
+    tri = mesh.triangles().reshape(-1, 3)
+    lo, hi = tri.min(0), tri.max(0)
+    cy, cz = (float(lo[1]) + float(hi[1])) / 2.0, (float(lo[2]) + float(hi[2])) / 2.0
+    ey, ez = (float(hi[1]) - float(lo[1])) / 2.0, (float(hi[2]) - float(lo[2])) / 2.0
+    depth = float(hi[0]) - float(lo[0])
+    side = 0.05 * min(ey, ez)
+    emitter = dict(origin=(float(lo[0]) - 1.5 * depth, cy - side / 2.0, cz - side / 2.0), edge_u=(0.0, side, 0.0), edge_v=(0.0, 0.0, side),
+                   points=spec["points"], rays_per_point=spec["rays_per_point"], belts=spec["belts"], seed=2026)
+    target = dict(origin=(float(hi[0]) + 4.0 * depth, cy - 3.0 * ey, cz - 3.0 * ez), edge_u=(0.0, 6.0 * ey, 0.0), edge_v=(0.0, 0.0, 6.0 * ez), bins=spec["bins"])
+    return spec, mesh, emitter, target
