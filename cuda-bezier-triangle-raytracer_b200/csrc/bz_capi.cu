@@ -217,6 +217,7 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
   if(desc.ray_count == 0u) { return BZ_OK; }
   BZ_CUDA(cudaMemsetAsync(lens->d_counter, 0, sizeof(unsigned long long), stream));
   desc.next_ray = lens->d_counter;
+  desc.one = 1.0f;
   bool const brute = (lens->mode == BZ_MODE_BRUTE);
   int grid;
   if(brute) {

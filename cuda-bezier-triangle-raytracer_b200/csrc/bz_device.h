@@ -78,6 +78,7 @@ struct bz_job {
   uint32_t *out_landing;       // nullable: per ray the bin, BZ_LAND_LOST or BZ_LAND_MISSED
   // all
   uint64_t  ray_count;       // primary rays of this call
+  float     one;             // 1.0f, as a run-time value (csrc/bz_trace.cu: packed sums)
   // work distribution: the job is cut into tiles handed to CTAs; RENDER: square blocks of tile_side x tile_side pixels
   // (tile_side a power of two, pixels of a tile in Morton order, tile_rays = tile_side^2 * spp); batch jobs: tile_rays
   // consecutive rays

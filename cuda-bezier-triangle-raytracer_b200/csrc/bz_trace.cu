@@ -108,6 +108,91 @@ __device__ __forceinline__ void bzw_load_newton_root(const float4 *p, bz_newton_
   t.dir_b = bz_v(w[30], w[31], w[32]);
 }
 
+#ifndef BZ_SCALAR_STAGE_B
+// ---- stage B on the packed FP32 pipe (sm_100a FMUL2 / FFMA2: two FP32 operations per issue slot) ----
+// The control points are kept as (x, y) pairs + z, the x and y components of bz_interpolate / bz_normal go through
+// __fmul2_rn / __ffma2_rn, z stays scalar.  Every component sees the same IEEE operations in the same order as in
+// bz_math.cuh, so the results are bit-identical (tests compare with the oracle).  A packed sum a + b is written
+// fma(b, one, a) with `one` = 1.0f read from the job descriptor: exactly a + b, and a form ptxas cannot contract -- it
+// fuses __fadd2_rn(__fmul2_rn(p, q), a) into one FFMA2 (a single rounding) even under -fmad=false.
+struct bzw_newton2 {
+  float2 xy[10];
+  float  z[10];
+  bzv3   dir_b;
+  float  one;
+};
+
+__device__ __forceinline__ float2 bzw_mul2(float2 a, float s) { return __fmul2_rn(a, make_float2(s, s)); }
+__device__ __forceinline__ float2 bzw_add2(float2 a, float2 b, float one) { return __ffma2_rn(b, make_float2(one, one), a); }
+
+__device__ __forceinline__ void bzw_load_newton2(const float4 *p, float one, bzw_newton2 &t) {
+  float w[36];
+#pragma unroll
+  for(int i = 0; i < 9; ++i) {
+    float4 r = __ldg(p + i);
+    w[4 * i] = r.x; w[4 * i + 1] = r.y; w[4 * i + 2] = r.z; w[4 * i + 3] = r.w;
+  }
+#pragma unroll
+  for(int i = 0; i < 10; ++i) { t.xy[i] = make_float2(w[3 * i], w[3 * i + 1]); t.z[i] = w[3 * i + 2]; }
+  t.dir_b = bz_v(w[30], w[31], w[32]);
+  t.one = one;
+}
+
+// bezierTriangle.cpp:105-121, operation for operation as bz_interpolate(const bz_newton_rec&, ...)
+__device__ __forceinline__ bzv3 bz_interpolate(const bzw_newton2 &t, const bzv3 &b) {
+  const float b0 = b.x, b1 = b.y, b2 = b.z;
+  const float q0 = b0 * b0, q1 = b1 * b1, q2 = b2 * b2;
+  const float one = t.one;
+#define BZW_T2(i, m, n) bzw_mul2(bzw_mul2(t.xy[i], m), n)
+  float2 a = bzw_add2(BZW_T2(0, b0, q0), BZW_T2(1, b1, q1), one);
+  a = bzw_add2(a, BZW_T2(2, b2, q2), one);
+  float2 g = bzw_add2(BZW_T2(3, b1, q0), BZW_T2(4, b0, q1), one);
+  g = bzw_add2(g, BZW_T2(5, b2, q1), one);
+  g = bzw_add2(g, BZW_T2(6, b1, q2), one);
+  g = bzw_add2(g, BZW_T2(7, b0, q2), one);
+  g = bzw_add2(g, BZW_T2(8, b2, q0), one);
+  a = bzw_add2(a, bzw_mul2(g, 3.0f), one);
+  a = bzw_add2(a, bzw_mul2(bzw_mul2(bzw_mul2(bzw_mul2(t.xy[9], b0), b1), b2), 6.0f), one);
+#undef BZW_T2
+  bzv3 r;
+  r.x = a.x;
+  r.y = a.y;
+  r.z = t.z[0] * b0 * q0 + t.z[1] * b1 * q1 + t.z[2] * b2 * q2 +
+        3.0f * (t.z[3] * b1 * q0 + t.z[4] * b0 * q1 + t.z[5] * b2 * q1 + t.z[6] * b1 * q2 + t.z[7] * b0 * q2 + t.z[8] * b2 * q0) +
+        t.z[9] * b0 * b1 * b2 * 6.0f;
+  return r;
+}
+
+// bezierTriangle.cpp:197-233, operation for operation as bz_normal(const bz_newton_rec&, ...)
+__device__ __forceinline__ bzv3 bz_normal(const bzw_newton2 &t, const bzv3 &b) {
+  const float b0 = b.x, b1 = b.y, b2 = b.z;
+  const float q0 = b0 * b0, q1 = b1 * b1, q2 = b2 * b2;
+  const float one = t.one;
+  // c = cp[i]*qa + cp[j]*qb + cp[k]*qc + 2*(cp[l]*m0*n0 + cp[m]*m1*n1 + cp[n]*m2*n2)
+#define BZW_C2(i, qa, j, qb, k, qc, l, m0, n0, m, m1, n1, n, m2, n2) \
+  bzw_add2(bzw_add2(bzw_add2(bzw_mul2(t.xy[i], qa), bzw_mul2(t.xy[j], qb), one), bzw_mul2(t.xy[k], qc), one), \
+           bzw_mul2(bzw_add2(bzw_add2(bzw_mul2(bzw_mul2(t.xy[l], m0), n0), bzw_mul2(bzw_mul2(t.xy[m], m1), n1), one), \
+                             bzw_mul2(bzw_mul2(t.xy[n], m2), n2), one), 2.0f), one)
+#define BZW_C1(i, qa, j, qb, k, qc, l, m0, n0, m, m1, n1, n, m2, n2) \
+  (t.z[i] * qa + t.z[j] * qb + t.z[k] * qc + 2.0f * (t.z[l] * m0 * n0 + t.z[m] * m1 * n1 + t.z[n] * m2 * n2))
+  const float2 c0 = BZW_C2(0, q0, 7, q2, 4, q1, 8, b0, b2, 3, b0, b1, 9, b2, b1);
+  const float2 c1 = BZW_C2(1, q1, 6, q2, 3, q0, 9, b0, b2, 4, b0, b1, 5, b1, b2);
+  const float2 c2 = BZW_C2(2, q2, 8, q0, 5, q1, 7, b0, b2, 6, b1, b2, 9, b0, b1);
+  const float z0 = BZW_C1(0, q0, 7, q2, 4, q1, 8, b0, b2, 3, b0, b1, 9, b2, b1);
+  const float z1 = BZW_C1(1, q1, 6, q2, 3, q0, 9, b0, b2, 4, b0, b1, 5, b1, b2);
+  const float z2 = BZW_C1(2, q2, 8, q0, 5, q1, 7, b0, b2, 6, b1, b2, 9, b0, b1);
+#undef BZW_C2
+#undef BZW_C1
+  // a = 1*c0 + 0*c1 + -1*c2 (dirA = (1, 0, -1), bezierTriangle.cpp:83); e = dirB . (c0, c1, c2)
+  const float2 a2 = bzw_add2(bzw_add2(bzw_mul2(c0, 1.0f), bzw_mul2(c1, 0.0f), one), bzw_mul2(c2, -1.0f), one);
+  const float2 e2 = bzw_add2(bzw_add2(bzw_mul2(c0, t.dir_b.x), bzw_mul2(c1, t.dir_b.y), one), bzw_mul2(c2, t.dir_b.z), one);
+  const bzv3 a = bz_v(a2.x, a2.y, 1.0f * z0 + 0.0f * z1 + -1.0f * z2);
+  const bzv3 e = bz_v(e2.x, e2.y, t.dir_b.x * z0 + t.dir_b.y * z1 + t.dir_b.z * z2);
+  const bzv3 n = bz_v(a.y * e.z - a.z * e.y, a.z * e.x - a.x * e.z, a.x * e.y - a.y * e.x);
+  return bz_normalized(n);
+}
+#endif
+
 // divider planes and neighbours: words 33..47, fetched after the root search (they are not live across its loop)
 __device__ __forceinline__ void bzw_load_newton_side(const float4 *p, bz_newton_rec &t) {
   const float4 carry = __ldg(p + 8), r9 = __ldg(p + 9), r10 = __ldg(p + 10), r11 = __ldg(p + 11);
@@ -609,8 +694,14 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           float cosine, distance;
           if(bz_stage_a(c, s, d, first_level, cosine, distance)) {
             bz_newton_rec t;
+#ifndef BZ_SCALAR_STAGE_B
+            bzw_newton2 t2;
+            bzw_load_newton2(T.newton + (size_t)patch * BZ_NEWTON_F4, J.one, t2);
+            if(bz_stage_b_root(c, t2, s, d, cosine, distance, hit)) {
+#else
             bzw_load_newton_root(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
             if(bz_stage_b_root(c, t, s, d, cosine, distance, hit)) {
+#endif
               bzw_load_newton_side(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
               bz_stage_b_side(t, d, hit);
             }
