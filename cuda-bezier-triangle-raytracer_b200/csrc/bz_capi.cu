@@ -124,7 +124,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
     const bz_patch &p = h_patches[i];
     bz_pack_cull(p, i, cull.data() + (size_t)i * 16u);
     float *w = newton.data() + (size_t)i * 48u;
-    std::memcpy(w, p.control, 30u * sizeof(float));
+    for(int k = 0; k < 10; ++k) { w[2 * k] = p.control[k][0]; w[2 * k + 1] = p.control[k][1]; w[20 + k] = p.control[k][2]; }    // (x, y) pairs on even words: the packed FP32 pipe reads them as aligned register pairs
     std::memcpy(w + 30, p.dir_b, 3u * sizeof(float));
     std::memcpy(w + 33, p.divider, 12u * sizeof(float));
     std::memcpy(w + 45, p.neighbours, 3u * sizeof(uint32_t));

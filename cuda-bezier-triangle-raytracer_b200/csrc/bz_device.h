@@ -4,7 +4,8 @@
 //   cull     4 float4 per patch, ORIGINAL patch order   stage-A record  (bezierTriangle.h:64,75,77-78)
 //            [0] plane n.xyz, k   [1] Binv row0.xyz, hIn   [2] Binv row1.xyz, hOut   [3] Binv row2.xyz, patch index bits
 //   newton  12 float4 per patch, ORIGINAL patch order   stage-B record  (bezierTriangle.h:65,68,73,80)
-//            words 0..29 control points, 30..32 dirB, 33..44 divider planes (n.xyz,k) x3, 45..47 neighbours
+//            words 0..19 (x, y) of the 10 control points (aligned pairs for FMUL2 / FFMA2), 20..29 their z, 30..32 dirB,
+//            33..44 divider planes (n.xyz,k) x3, 45..47 neighbours
 //   leaf     4 float4 per leaf slot: the cull records again, in BVH leaf order, followed by the "wide"
 //            segment (tested directly only by rays starting beyond origin_limit) and the "always"
 //            segment (patches the cull cannot bound, tested for every ray)

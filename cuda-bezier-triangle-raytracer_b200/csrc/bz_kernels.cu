@@ -64,7 +64,7 @@ __device__ __forceinline__ void bz_load_newton(const float4 *base, uint32_t inde
     w[4 * i] = r.x; w[4 * i + 1] = r.y; w[4 * i + 2] = r.z; w[4 * i + 3] = r.w;
   }
 #pragma unroll
-  for(int i = 0; i < 10; ++i) { t.cp[i] = bz_v(w[3 * i], w[3 * i + 1], w[3 * i + 2]); }
+  for(int i = 0; i < 10; ++i) { t.cp[i] = bz_v(w[2 * i], w[2 * i + 1], w[20 + i]); }
   t.dir_b = bz_v(w[30], w[31], w[32]);
 #pragma unroll
   for(int i = 0; i < 3; ++i) {

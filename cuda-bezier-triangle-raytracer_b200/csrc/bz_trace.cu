@@ -95,7 +95,8 @@ __device__ __forceinline__ void bzw_unpack_cull(const float4 *p, bz_cull_rec &c,
   index = __float_as_uint(r3.w);
 }
 
-// control points and dirB: words 0..32 of the stage-B record (word 33..35 of float4 #8 are the first divider normal)
+// control points and dirB: words 0..32 of the stage-B record: (x, y) of the ten control points, their z, dirB
+// (words 33..35 of float4 #8 are the first divider normal)
 __device__ __forceinline__ void bzw_load_newton_root(const float4 *p, bz_newton_rec &t) {
   float w[36];
 #pragma unroll
@@ -104,7 +105,7 @@ __device__ __forceinline__ void bzw_load_newton_root(const float4 *p, bz_newton_
     w[4 * i] = r.x; w[4 * i + 1] = r.y; w[4 * i + 2] = r.z; w[4 * i + 3] = r.w;
   }
 #pragma unroll
-  for(int i = 0; i < 10; ++i) { t.cp[i] = bz_v(w[3 * i], w[3 * i + 1], w[3 * i + 2]); }
+  for(int i = 0; i < 10; ++i) { t.cp[i] = bz_v(w[2 * i], w[2 * i + 1], w[20 + i]); }
   t.dir_b = bz_v(w[30], w[31], w[32]);
 }
 
@@ -133,7 +134,7 @@ __device__ __forceinline__ void bzw_load_newton2(const float4 *p, float one, bzw
     w[4 * i] = r.x; w[4 * i + 1] = r.y; w[4 * i + 2] = r.z; w[4 * i + 3] = r.w;
   }
 #pragma unroll
-  for(int i = 0; i < 10; ++i) { t.xy[i] = make_float2(w[3 * i], w[3 * i + 1]); t.z[i] = w[3 * i + 2]; }
+  for(int i = 0; i < 10; ++i) { t.xy[i] = make_float2(w[2 * i], w[2 * i + 1]); t.z[i] = w[20 + i]; }
   t.dir_b = bz_v(w[30], w[31], w[32]);
   t.one = one;
 }
