@@ -246,7 +246,8 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
       desc.tile_side = side;
       desc.tile_rays = side * side * spp;
       desc.tiles_x = (desc.camera.width + side - 1u) / side;
-      desc.tile_count = (uint64_t)desc.tiles_x * ((desc.rows + side - 1u) / side);
+      desc.tiles_y = (desc.rows + side - 1u) / side;
+      desc.tile_count = (uint64_t)desc.tiles_x * desc.tiles_y;
     }
     else {
       desc.tile_side = 0u;

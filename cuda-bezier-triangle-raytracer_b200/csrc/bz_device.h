@@ -84,7 +84,7 @@ struct bz_job {
   // (tile_side a power of two, pixels of a tile in Morton order, tile_rays = tile_side^2 * spp); batch jobs: tile_rays
   // consecutive rays
   uint32_t  rows;            // RENDER: image rows of this call (local rows of the band)
-  uint32_t  tile_side, tile_rays, tiles_x;
+  uint32_t  tile_side, tile_rays, tiles_x, tiles_y;
   uint32_t  div_spp[2], div_strata[2], div_stripe[2];   // reciprocals for n / spp, n / strata, n / stripe_rows (bzw_div)
   float     two_over_w, two_over_h;                      // 2.0f / (float)width, 2.0f / (float)height
   uint64_t  tile_count;

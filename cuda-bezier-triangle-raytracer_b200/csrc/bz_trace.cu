@@ -419,7 +419,12 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             if(JOB == BZ_JOB_RENDER) {
               // (divisions by per-job constants are multiplications by the host's reciprocals, bz_job::div_*)
               const uint32_t inside = bzw_div(at, J.div_spp), sample = at - inside * spp;   // pixel of the tile in Morton order, sample of the pixel
-              const uint32_t tile_y = tile / J.tiles_x, tile_x = tile - tile_y * J.tiles_x;
+              // tile rows are taken from the outside in (top, bottom, second, second to last, ...): the costliest packets of a
+              // frame sit on the silhouette of the body (grazing rays meet many leaf boxes and walk per lane), the centre rows
+              // are uniform -- ending on them keeps the tail of the persistent grid short, which matters for the short
+              // per-GPU launches of a row-sharded frame
+              const uint32_t turn = tile / J.tiles_x, tile_x = tile - turn * J.tiles_x;
+              const uint32_t tile_y = ((turn & 1u) == 0u) ? (turn >> 1) : (J.tiles_y - 1u - (turn >> 1));
               const uint32_t px = tile_x * J.tile_side + bzw_even_bits(inside), row = tile_y * J.tile_side + bzw_even_bits(inside >> 1);
               valid = valid && px < J.camera.width && row < J.rows;
               if(valid) {
