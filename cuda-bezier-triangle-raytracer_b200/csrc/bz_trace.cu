@@ -627,13 +627,15 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           float cosine, distance; \
           const bool pass = live && bz_stage_a(c, s, d, true, cosine, distance); \
           const uint32_t passed = __ballot_sync(0xffffffffu, pass); \
-          if(pass) { \
-            const uint32_t at = level + __popc(passed & below); \
-            P.qb_patch[at] = patch; \
-            P.qb_loop[at] = patch; \
-            P.qb_slot[at] = (uint8_t)(slot | 0x80u); \
+          if(passed != 0u) {                 /* (most records are met by no ray of the packet) */ \
+            if(pass) { \
+              const uint32_t at = level + __popc(passed & below); \
+              P.qb_patch[at] = patch; \
+              P.qb_loop[at] = patch; \
+              P.qb_slot[at] = (uint8_t)(slot | 0x80u); \
+            } \
+            level += __popc(passed); \
           } \
-          level += __popc(passed); \
           ++tested; }
         while(cand_at < cand_n && level <= BZ_QB_CAP - 64u) {
           BZW_FETCH(a0, a1, a2, a3)

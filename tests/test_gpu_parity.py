@@ -78,7 +78,8 @@ def test_refract_edge_cases(bz, oracle_built):
 
 
 @pytest.mark.parametrize("name,w,h,strata,crossings", [("sphere16x8", 160, 120, 1, 2), ("sphere16x8", 64, 48, 4, 2), ("robot", 96, 64, 2, 8),
-                                                      ("sphere16x8", 131, 77, 3, 2), ("ellipsoid64x32", 67, 45, 1, 2)])   # ragged edge tiles, spp not a power of two
+                                                      ("sphere16x8", 131, 77, 3, 2), ("ellipsoid64x32", 67, 45, 1, 2),   # ragged edge tiles, spp not a power of two
+                                                      ("sphere16x8", 50, 37, 5, 2), ("sphere16x8", 9, 5, 12, 2)])         # tile rays not a multiple of 32; a 2x2-pixel tile
 def test_render_pixel_exact_vs_reference(bz, oracle_built, name, w, h, strata, crossings):
     import bzref
     mesh, bezier, patches = common.ref_config(name)
