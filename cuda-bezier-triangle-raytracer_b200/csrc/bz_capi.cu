@@ -45,7 +45,7 @@ struct bz_lens {
   int        sm_count;
   uint32_t   mode;
   bz_tables  tables;
-  float4    *d_cull, *d_newton, *d_leaf, *d_nodes, *d_packet;
+  float4    *d_cull, *d_newton, *d_leaf, *d_pairs, *d_nodes, *d_packet;
   unsigned long long *d_counter;      // work counter of the persistent kernel
   uint32_t  *d_accum;                 // render scratch: one u32 per pixel of the largest band so far
   size_t     accum_pixels;
@@ -91,7 +91,7 @@ uint32_t bz_sizeof_stats(void) { return (uint32_t)sizeof(bz_stats); }
 int bz_lens_destroy(bz_lens *lens) {
   if(lens == nullptr) { return BZ_OK; }
   cudaSetDevice(lens->device);
-  cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_nodes); cudaFree(lens->d_packet);
+  cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_pairs); cudaFree(lens->d_nodes); cudaFree(lens->d_packet);
   cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch); cudaFree(lens->d_illum);
   if(lens->ev_begin) { cudaEventDestroy(lens->ev_begin); }
   if(lens->ev_end) { cudaEventDestroy(lens->ev_end); }
@@ -158,6 +158,17 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   e = upload(cull, &lens->d_cull);
   if(e == cudaSuccess) { e = upload(newton, &lens->d_newton); }
   if(e == cudaSuccess) { e = upload(leaf, &lens->d_leaf); }
+  {
+    // slot j of `pairs` = records j and j + 1 of `leaf`, word by word (the last slot pairs with a record no ray can meet)
+    std::vector<float> pairs(slot2patch.size() * 32u, 0.0f);
+    for(size_t k = 0u; k < slot2patch.size(); ++k) {
+      for(size_t w = 0u; w < 16u; ++w) {
+        pairs[k * 32u + 2u * w] = leaf[k * 16u + w];
+        pairs[k * 32u + 2u * w + 1u] = (k + 1u < slot2patch.size()) ? leaf[(k + 1u) * 16u + w] : 0.0f;
+      }
+    }
+    if(e == cudaSuccess) { e = upload(pairs, &lens->d_pairs); }
+  }
   if(e == cudaSuccess) { e = upload(bvh.nodes, &lens->d_nodes); }
   if(e == cudaSuccess) { e = upload(bvh.packet_nodes, &lens->d_packet); }
   if(e == cudaSuccess) { e = cudaMalloc((void**)&lens->d_counter, 64u); }
@@ -171,6 +182,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   lens->tables.cull = lens->d_cull;
   lens->tables.newton = lens->d_newton;
   lens->tables.leaf = lens->d_leaf;
+  lens->tables.pairs = lens->d_pairs;
   lens->tables.nodes = lens->d_nodes;
   lens->tables.packet = (const float*)lens->d_packet;
   lens->tables.packet_count = (uint32_t)(bvh.packet_nodes.size() / 224u);

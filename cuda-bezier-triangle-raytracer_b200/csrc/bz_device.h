@@ -12,6 +12,8 @@
 //   packet   7 x 32 words per node of the same hierarchy collapsed to 32 children per node (one lane per child):
 //            lo.x[32] lo.y[32] lo.z[32] hi.x[32] hi.y[32] hi.z[32] code[32]; code 0 = empty child, bit 31 = inner child
 //            (low bits: node index), else first_slot << 3 | count
+//   pairs    8 float4 per leaf slot j: the leaf records j and j + 1 interleaved word by word, so that the packet form of
+//            stage A tests two records per trip with FMUL2 / FFMA2 (every float4 = two aligned (A, B) register pairs)
 //   nodes    2 float4 per node of the binary cull hierarchy, depth-first order:
 //            [0] box lo.xyz, skip link (index of the first node after this subtree, taken when the box is missed)
 //            [1] box hi.xyz, leaf code (0: inner node, its first child is the next node; else first_slot << 3 | count)
@@ -31,6 +33,7 @@ struct bz_tables {
   const float4 *cull;
   const float4 *newton;
   const float4 *leaf;
+  const float4 *pairs;     // 8 float4 per leaf slot j: records j and j + 1 of `leaf` interleaved word by word (packet stage A)
   const float4 *nodes;
   const float  *packet;    // the hierarchy again, 32 children per node, 7 x 32 words per node (host/bz_bvh.h)
   uint32_t packet_count;

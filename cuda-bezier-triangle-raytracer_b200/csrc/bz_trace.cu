@@ -610,41 +610,62 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
         const uint32_t below = (1u << lane) - 1u;
         uint32_t level = qb;                  // warp-uniform copy of the level of queue B
         uint32_t tested = 0u;
-        // all addresses are the same for the whole warp (broadcast loads); no software pipelining: holding a second record
-        // in registers costs more in spills around stage B than the L1 latency it hides
-        float4 a0, a1, a2, a3;
-#define BZW_FETCH(r0, r1, r2, r3) { \
-          const float4 *rec = T.leaf + (size_t)((P.cand[cand_at] >> 3) + cand_sub) * BZ_CULL_F4; \
-          r0 = __ldg(rec); r1 = __ldg(rec + 1); r2 = __ldg(rec + 2); r3 = __ldg(rec + 3); }
-#define BZW_ADVANCE() { if(++cand_sub == (P.cand[cand_at] & 7u)) { cand_sub = 0u; ++cand_at; } }
-#define BZW_TEST(r0, r1, r2, r3) { \
-          bz_cull_rec c; \
-          c.n = bz_v(r0.x, r0.y, r0.z); c.k = r0.w; \
-          c.b0 = bz_v(r1.x, r1.y, r1.z); c.h_in = r1.w; \
-          c.b1 = bz_v(r2.x, r2.y, r2.z); c.h_out = r2.w; \
-          c.b2 = bz_v(r3.x, r3.y, r3.z); \
-          const uint32_t patch = __float_as_uint(r3.w); \
-          float cosine, distance; \
-          const bool pass = live && bz_stage_a(c, s, d, true, cosine, distance); \
-          const uint32_t passed = __ballot_sync(0xffffffffu, pass); \
-          if(passed != 0u) {                 /* (most records are met by no ray of the packet) */ \
-            if(pass) { \
-              const uint32_t at = level + __popc(passed & below); \
-              P.qb_patch[at] = patch; \
-              P.qb_loop[at] = patch; \
-              P.qb_slot[at] = (uint8_t)(slot | 0x80u); \
-            } \
-            level += __popc(passed); \
-          } \
-          ++tested; }
+        // Two records per trip on the packed FP32 pipe: record j of the `pairs` table holds leaf records j and j + 1
+        // interleaved word by word, so every float4 is two aligned (A, B) register pairs.  All addresses are the same for
+        // the whole warp (broadcast loads).  Each half sees the operations of bz_stage_a in their order; the two IEEE
+        // divisions stay scalar.
+        const float one = J.one;
         while(cand_at < cand_n && level <= BZ_QB_CAP - 64u) {
-          BZW_FETCH(a0, a1, a2, a3)
-          BZW_ADVANCE()
-          BZW_TEST(a0, a1, a2, a3)
+          const uint32_t code = P.cand[cand_at];
+          const uint32_t left = (code & 7u) - cand_sub;             // records of this entry still to be tested
+          const float4 *rec = T.pairs + (size_t)((code >> 3) + cand_sub) * (2u * BZ_CULL_F4);
+          const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2), r3 = __ldg(rec + 3);
+          const float4 r4 = __ldg(rec + 4), r5 = __ldg(rec + 5), r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
+          cand_sub += min(left, 2u);
+          if(left <= 2u) { cand_sub = 0u; ++cand_at; }
+          tested += min(left, 2u);
+          // words of a cull record: 0-2 n, 3 k, 4-6 Binv row 0, 7 hIn, 8-10 row 1, 11 hOut, 12-14 row 2, 15 patch
+          const float2 nx = make_float2(r0.x, r0.y), ny = make_float2(r0.z, r0.w), nz = make_float2(r1.x, r1.y), kk = make_float2(r1.z, r1.w);
+          const float2 cosine = bzw_add2(bzw_mul2(nx, d.x), bzw_add2(bzw_mul2(ny, d.y), bzw_mul2(nz, d.z), one), one);         // bz_dot(d, n)
+          const float2 along = bzw_add2(bzw_mul2(nx, s.x), bzw_add2(bzw_mul2(ny, s.y), bzw_mul2(nz, s.z), one), one);          // bz_dot(n, s)
+          const float2 above = __ffma2_rn(along, make_float2(-one, -one), kk);                                                  // k - bz_dot(n, s)
+          bool pass_a = live && fabsf(cosine.x) >= BZ_PLANE_EPSILON;
+          bool pass_b = live && left >= 2u && fabsf(cosine.y) >= BZ_PLANE_EPSILON;
+          float2 distance = make_float2(0.0f, 0.0f);
+          if(pass_a) { distance.x = above.x / cosine.x; }
+          if(pass_b) { distance.y = above.y / cosine.y; }
+          pass_a = pass_a && distance.x > 0.0f && fabsf(distance.x) > -r3.z && fabsf(distance.x) > r5.z;     // hIn (word 7), hOut (word 11)
+          pass_b = pass_b && distance.y > 0.0f && fabsf(distance.y) > -r3.w && fabsf(distance.y) > r5.w;
+          if(__ballot_sync(0xffffffffu, pass_a || pass_b) != 0u) {
+            const float2 px = __ffma2_rn(bzw_mul2(distance, d.x), make_float2(one, one), make_float2(s.x, s.x));               // s + distance * d
+            const float2 py = __ffma2_rn(bzw_mul2(distance, d.y), make_float2(one, one), make_float2(s.y, s.y));
+            const float2 pz = __ffma2_rn(bzw_mul2(distance, d.z), make_float2(one, one), make_float2(s.z, s.z));
+#define BZW_ROW(x, y, z) bzw_add2(__fmul2_rn(x, px), bzw_add2(__fmul2_rn(y, py), __fmul2_rn(z, pz), one), one)             /* bz_dot(row, p) */
+            const float2 b0 = BZW_ROW(make_float2(r2.x, r2.y), make_float2(r2.z, r2.w), make_float2(r3.x, r3.y));
+            const float2 b1 = BZW_ROW(make_float2(r4.x, r4.y), make_float2(r4.z, r4.w), make_float2(r5.x, r5.y));
+            const float2 b2 = BZW_ROW(make_float2(r6.x, r6.y), make_float2(r6.z, r6.w), make_float2(r7.x, r7.y));
+#undef BZW_ROW
+            pass_a = pass_a && b0.x >= 0.0f && b0.x <= 1.0f && b1.x >= 0.0f && b1.x <= 1.0f && b2.x >= 0.0f && b2.x <= 1.0f;
+            pass_b = pass_b && b0.y >= 0.0f && b0.y <= 1.0f && b1.y >= 0.0f && b1.y <= 1.0f && b2.y >= 0.0f && b2.y <= 1.0f;
+            const uint32_t passed_a = __ballot_sync(0xffffffffu, pass_a), passed_b = __ballot_sync(0xffffffffu, pass_b);
+            if((passed_a | passed_b) != 0u) {
+              if(pass_a) {
+                const uint32_t at = level + __popc(passed_a & below);
+                P.qb_patch[at] = __float_as_uint(r7.z);
+                P.qb_loop[at] = __float_as_uint(r7.z);
+                P.qb_slot[at] = (uint8_t)(slot | 0x80u);
+              }
+              level += __popc(passed_a);
+              if(pass_b) {
+                const uint32_t at = level + __popc(passed_b & below);
+                P.qb_patch[at] = __float_as_uint(r7.w);
+                P.qb_loop[at] = __float_as_uint(r7.w);
+                P.qb_slot[at] = (uint8_t)(slot | 0x80u);
+              }
+              level += __popc(passed_b);
+            }
+          }
         }
-#undef BZW_FETCH
-#undef BZW_ADVANCE
-#undef BZW_TEST
         if(lane == 0u) { P.qb_n = level; }
         BZW_COUNT(BZC_STAGE_A, tested * __popc(__ballot_sync(0xffffffffu, live)));
         continue;
