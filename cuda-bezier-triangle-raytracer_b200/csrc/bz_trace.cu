@@ -170,12 +170,13 @@ __device__ __forceinline__ bzv3 bz_normal(const bzw_newton2 &t, const bzv3 &b) {
   const float q0 = b0 * b0, q1 = b1 * b1, q2 = b2 * b2;
   const float one = t.one;
   // c = cp[i]*qa + cp[j]*qb + cp[k]*qc + 2*(cp[l]*m0*n0 + cp[m]*m1*n1 + cp[n]*m2*n2)
+  // (X + 2*S is one fma(S, 2, X): doubling is exact, so the single rounding is the reference's rounding of the sum)
 #define BZW_C2(i, qa, j, qb, k, qc, l, m0, n0, m, m1, n1, n, m2, n2) \
-  bzw_add2(bzw_add2(bzw_add2(bzw_mul2(t.xy[i], qa), bzw_mul2(t.xy[j], qb), one), bzw_mul2(t.xy[k], qc), one), \
-           bzw_mul2(bzw_add2(bzw_add2(bzw_mul2(bzw_mul2(t.xy[l], m0), n0), bzw_mul2(bzw_mul2(t.xy[m], m1), n1), one), \
-                             bzw_mul2(bzw_mul2(t.xy[n], m2), n2), one), 2.0f), one)
+  __ffma2_rn(bzw_add2(bzw_add2(bzw_mul2(bzw_mul2(t.xy[l], m0), n0), bzw_mul2(bzw_mul2(t.xy[m], m1), n1), one), \
+                      bzw_mul2(bzw_mul2(t.xy[n], m2), n2), one), make_float2(2.0f, 2.0f), \
+             bzw_add2(bzw_add2(bzw_mul2(t.xy[i], qa), bzw_mul2(t.xy[j], qb), one), bzw_mul2(t.xy[k], qc), one))
 #define BZW_C1(i, qa, j, qb, k, qc, l, m0, n0, m, m1, n1, n, m2, n2) \
-  (t.z[i] * qa + t.z[j] * qb + t.z[k] * qc + 2.0f * (t.z[l] * m0 * n0 + t.z[m] * m1 * n1 + t.z[n] * m2 * n2))
+  __fmaf_rn(t.z[l] * m0 * n0 + t.z[m] * m1 * n1 + t.z[n] * m2 * n2, 2.0f, t.z[i] * qa + t.z[j] * qb + t.z[k] * qc)
   const float2 c0 = BZW_C2(0, q0, 7, q2, 4, q1, 8, b0, b2, 3, b0, b1, 9, b2, b1);
   const float2 c1 = BZW_C2(1, q1, 6, q2, 3, q0, 9, b0, b2, 4, b0, b1, 5, b1, b2);
   const float2 c2 = BZW_C2(2, q2, 8, q0, 5, q1, 7, b0, b2, 6, b1, b2, 9, b0, b1);
@@ -185,9 +186,10 @@ __device__ __forceinline__ bzv3 bz_normal(const bzw_newton2 &t, const bzv3 &b) {
 #undef BZW_C2
 #undef BZW_C1
   // a = 1*c0 + 0*c1 + -1*c2 (dirA = (1, 0, -1), bezierTriangle.cpp:83); e = dirB . (c0, c1, c2)
-  const float2 a2 = bzw_add2(bzw_add2(bzw_mul2(c0, 1.0f), bzw_mul2(c1, 0.0f), one), bzw_mul2(c2, -1.0f), one);
+  // (1*c0 is c0; c0 + 0*c1 is one fma(c1, 0, c0): the product is an exact signed zero, or NaN; adding -1*c2 is subtracting c2)
+  const float2 a2 = __ffma2_rn(c2, make_float2(-one, -one), __ffma2_rn(c1, make_float2(0.0f, 0.0f), c0));
   const float2 e2 = bzw_add2(bzw_add2(bzw_mul2(c0, t.dir_b.x), bzw_mul2(c1, t.dir_b.y), one), bzw_mul2(c2, t.dir_b.z), one);
-  const bzv3 a = bz_v(a2.x, a2.y, 1.0f * z0 + 0.0f * z1 + -1.0f * z2);
+  const bzv3 a = bz_v(a2.x, a2.y, __fmaf_rn(z1, 0.0f, z0) - z2);
   const bzv3 e = bz_v(e2.x, e2.y, t.dir_b.x * z0 + t.dir_b.y * z1 + t.dir_b.z * z2);
   const bzv3 n = bz_v(a.y * e.z - a.z * e.y, a.z * e.x - a.x * e.z, a.x * e.y - a.y * e.x);
   return bz_normalized(n);
