@@ -365,6 +365,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
   const uint32_t spp = J.camera.strata * J.camera.strata;
   const uint32_t direct_end = T.always_first + T.always_count;
   bool exhausted = false;                    // warp-uniform: the global ray counter has run past the end
+  uint32_t tally = 0u, tally_turns = 0u;     // per lane: packed event counters of the resolve step; warp-uniform: turns since their last fold
 
 #pragma unroll
   for(int g = 0; g < BZ_GROUPS; ++g) { P.state[g * 32 + lane] = 0u; }
@@ -771,7 +772,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
     for(int g = 0; g < BZ_GROUPS; ++g) {
       const uint32_t slot = (uint32_t)g * 32u + lane;
       const uint32_t st = P.state[slot];
-      uint32_t events = 0u;                  // bit 0 Snell block reached, 1 entered, 2 exited, 3 lost
+      uint32_t events = 0u;                  // byte 0 Snell block reached, 1 entered, 2 exited, 3 lost
       if((st & 1u) != 0u) {
       uint32_t expected = (st >> 1) & 3u;
       uint32_t crossings = st >> 4;
@@ -814,7 +815,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
         if(status != BZ_STATUS_NONE) {
           s = hit.point;
           d = refracted;
-          events |= (status == BZ_STATUS_INSIDE) ? 2u : 4u;
+          events |= (status == BZ_STATUS_INSIDE) ? 0x100u : 0x10000u;
         }
         if(JOB == BZ_JOB_REFRACT) {
           const unsigned long long ray_id = ((unsigned long long)P.id_hi[slot] << 32) | P.id_lo[slot];
@@ -838,7 +839,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             }
             else {                                  // entered and never left
               value = (JOB == BZ_JOB_TARGET) ? BZ_LAND_LOST : J.scene.value_lost;
-              events |= 8u;
+              events |= 0x1000000u;
             }
             if(JOB == BZ_JOB_TARGET) {
               if(value < BZ_LAND_MISSED) { atomicAdd(J.bins + value, 1u); }
@@ -858,15 +859,25 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
       P.state[slot] = live ? (1u | (expected << 1) | (crossings << 4)) : 0u;
       }
       if(JOB != BZ_JOB_INTERSECT) {
-        BZW_COUNT(BZC_SNELL, __popc(__ballot_sync(0xffffffffu, (events & 1u) != 0u)));
-        BZW_COUNT(BZC_ENTER, __popc(__ballot_sync(0xffffffffu, (events & 2u) != 0u)));
-        BZW_COUNT(BZC_EXIT, __popc(__ballot_sync(0xffffffffu, (events & 4u) != 0u)));
-        BZW_COUNT(BZC_LOST, __popc(__ballot_sync(0xffffffffu, (events & 8u) != 0u)));
+        // four event counters per lane in the bytes of one register, folded into the warp's counters every 255 turns
+        tally += events;
+        if(++tally_turns == 255u) {
+          BZW_COUNT(BZC_SNELL, __reduce_add_sync(0xffffffffu, tally & 0xffu));
+          BZW_COUNT(BZC_ENTER, __reduce_add_sync(0xffffffffu, (tally >> 8) & 0xffu));
+          BZW_COUNT(BZC_EXIT, __reduce_add_sync(0xffffffffu, (tally >> 16) & 0xffu));
+          BZW_COUNT(BZC_LOST, __reduce_add_sync(0xffffffffu, tally >> 24));
+          tally = 0u;
+          tally_turns = 0u;
+        }
       }
     }
   }
 
   // ---- work counters: one atomic per warp and counter ----
+  BZW_COUNT(BZC_SNELL, __reduce_add_sync(0xffffffffu, tally & 0xffu));
+  BZW_COUNT(BZC_ENTER, __reduce_add_sync(0xffffffffu, (tally >> 8) & 0xffu));
+  BZW_COUNT(BZC_EXIT, __reduce_add_sync(0xffffffffu, (tally >> 16) & 0xffu));
+  BZW_COUNT(BZC_LOST, __reduce_add_sync(0xffffffffu, tally >> 24));
   __syncwarp();
   if(J.stats != nullptr && lane < BZ_NSTAT && P.count[lane] != 0ull) { atomicAdd(J.stats + lane, P.count[lane]); }
 }
