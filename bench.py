@@ -305,7 +305,7 @@ def main_ours(args, name):
             "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / (k_ms * 1e-3) / 1e9, "peak_gbs": hbm_peak,
                     "frac": hbm_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback"},
         }
-        launches_per_step = 2 + (1 if world > 1 else 0)       # trace + resolve (+ assemble on rank 0)
+        launches_per_step = lens.last_kernel_launches() + (1 if world > 1 else 0)       # sky + trace + resolve (+ assemble on rank 0)
         line = {
             "metric": "Mrays/s", "value": frame_rays / (ms_per_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,

@@ -166,6 +166,7 @@ SIGNATURES = {
     "bz_bezier_split_thick": (_int, [_vp, C.POINTER(_vp)]),
     "bz_lens_create_from_bezier": (_int, [_vp, _f, _int, C.POINTER(_vp)]),
     "bz_last_kernel_ms": (_int, [_vp, C.POINTER(_f)]),
+    "bz_last_kernel_launches": (_int, [_vp, C.POINTER(_u32)]),
     "bz_sizeof_emitter": (_u32, []),
     "bz_sizeof_target": (_u32, []),
     "bz_hemisphere_patches": (_int, [_u32, C.POINTER(_u32), _vp, _vp]),
@@ -427,6 +428,11 @@ class BezierLens:
         ms = _f(0.0)
         _check(self.lib.bz_last_kernel_ms(self.h, C.byref(ms)))
         return ms.value
+
+    def last_kernel_launches(self):
+        count = _u32(0)
+        _check(self.lib.bz_last_kernel_launches(self.h, C.byref(count)))
+        return count.value
 
     # ---- host-buffer entry points (numpy in, numpy out; copies inside the call) ----
 

@@ -23,6 +23,7 @@ cudaError_t bz_launch_assemble(const uint8_t *bands, uint32_t band_rows, uint32_
 cudaError_t bz_launch_fma_probe(float *sink, uint32_t iters, int grid, cudaStream_t stream);
 int bz_trace_threads(void);
 cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream);
+cudaError_t bz_launch_sky(const bz_job &desc, const uint32_t *d_tiles, uint32_t count, cudaStream_t stream);
 cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta);
 cudaError_t bz_launch_emit(const bz_emitter &em, const bz_belts &belts, uint64_t first, uint64_t count, float *start, float *dir, uint32_t *patch,
                            cudaStream_t stream);
@@ -57,7 +58,20 @@ struct bz_lens {
   cudaStream_t last_stream;
   bool       timed;
   uint32_t   bvh_depth;
+  // RENDER: which tiles of a frame can meet the lens (bz_plan_tiles)
+  std::vector<float> outline;         // up to BZ_OUTLINE_BOXES boxes of the cull hierarchy that cover every patch: lo.xyz hi.xyz each
+  struct {
+    bool      valid;
+    bz_camera camera;
+    uint32_t  row0, rows, stripe_rows, rank, ranks, side;
+    uint32_t  lens_count, sky_count;  // d_tiles = lens tiles in hand-out order, then sky tiles
+  } plan;
+  uint32_t  *d_tiles;
+  size_t     tiles_capacity;
+  uint32_t   launches;                // kernels of the most recent call
 };
+
+static void bz_outline_boxes(const bz_bvh &bvh, std::vector<float> &out);
 
 static int bz_check_device(int device) {
   int count = 0;
@@ -92,7 +106,7 @@ int bz_lens_destroy(bz_lens *lens) {
   if(lens == nullptr) { return BZ_OK; }
   cudaSetDevice(lens->device);
   cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_pairs); cudaFree(lens->d_nodes); cudaFree(lens->d_packet);
-  cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch); cudaFree(lens->d_illum);
+  cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch); cudaFree(lens->d_illum); cudaFree(lens->d_tiles);
   if(lens->ev_begin) { cudaEventDestroy(lens->ev_begin); }
   if(lens->ev_end) { cudaEventDestroy(lens->ev_end); }
   delete lens;
@@ -135,11 +149,11 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   std::vector<float> leaf(slot2patch.size() * 16u);
   for(size_t k = 0u; k < slot2patch.size(); ++k) { bz_pack_cull(h_patches[slot2patch[k]], slot2patch[k], leaf.data() + k * 16u); }
 
-  bz_lens *lens = new bz_lens();
-  std::memset(lens, 0, sizeof(*lens));
+  bz_lens *lens = new bz_lens();      // (value-initialised: every plain member is zero)
   lens->device = device;
   lens->mode = BZ_MODE_CULLED;
   lens->bvh_depth = bvh.depth;
+  bz_outline_boxes(bvh, lens->outline);
   cudaDeviceProp prop;
   cudaError_t e = cudaGetDeviceProperties(&prop, device);
   if(e != cudaSuccess) { delete lens; return bz_fail(BZ_ERR_CUDA, cudaGetErrorString(e)); }
@@ -223,15 +237,139 @@ int bz_lens_info(const bz_lens *lens, uint32_t out[4]) {
 
 // ------------------------------------------------------------------ launches ----
 
+// ---- RENDER: which tiles of the frame can meet the lens ----
+// A ray that misses a box of the cull hierarchy (grown by the walk's slack) fails stage A of every patch below it -- that
+// is the hierarchy's own guarantee.  bz_plan_tiles projects a few hundred boxes that together cover every patch (the
+// "outline", picked at bz_lens_create) onto the image; a tile no projected box touches has no ray that can meet the lens:
+// every refract() of its rays is cNone and bz_sky_kernel shades it, the trace kernel gets the other tiles only.
+//   pinhole: ray = eye + t M (a, b, 1), M = [right | up | forward], t > 0: it meets a box only if (a, b) lies in the
+//            projection (x / z, y / z) of Q = M^-1 (box - eye), a convex body -- within the bounding rectangle of its 8
+//            projected corners when all of them have z > 0; a box with all z <= 0 lies behind every ray;
+//   orthographic: ray = eye + M (a, b, t): (a, b) within the bounding rectangle of the (x, y) of Q's corners.
+// The boxes are grown by twice the packet walk's own margin, the rectangles by two whole pixels (the float rounding of
+// (a, b) and of the normalised direction is below 1e-2 pixel).  Anything unusual -> no plan: every tile is traced.
+#define BZ_OUTLINE_BOXES 1024u
+
+// boxes of the hierarchy covering every patch: the root, repeatedly replacing the largest inner box by its two children
+static void bz_outline_boxes(const bz_bvh &bvh, std::vector<float> &out) {
+  out.clear();
+  size_t const count = bvh.nodes.size() / 8u;
+  if(count == 0u) { return; }
+  auto word = [&](size_t node, int k) { uint32_t w; std::memcpy(&w, &bvh.nodes[node * 8u + k], sizeof(w)); return w; };
+  auto area = [&](size_t node) {
+    const float *p = &bvh.nodes[node * 8u];
+    double const dx = (double)p[4] - p[0], dy = (double)p[5] - p[1], dz = (double)p[6] - p[2];
+    return dx * dy + dy * dz + dz * dx;
+  };
+  std::vector<std::pair<double, size_t>> heap;      // (area, node) of the inner boxes still splittable
+  std::vector<size_t> kept;
+  if(word(0u, 7) == 0u) { heap.push_back({ area(0u), 0u }); } else { kept.push_back(0u); }
+  while(!heap.empty() && kept.size() + heap.size() < BZ_OUTLINE_BOXES) {
+    std::pop_heap(heap.begin(), heap.end());
+    size_t const node = heap.back().second;
+    heap.pop_back();
+    size_t const left = node + 1u, right = word(left, 3);      // depth-first order: first child follows, its skip link is the sibling
+    for(size_t child : { left, right }) {
+      if(child >= count) { out.clear(); return; }              // (cannot happen for a table bz_build_bvh made)
+      if(word(child, 7) == 0u) { heap.push_back({ area(child), child }); std::push_heap(heap.begin(), heap.end()); }
+      else { kept.push_back(child); }
+    }
+  }
+  for(auto const &entry : heap) { kept.push_back(entry.second); }
+  for(size_t node : kept) {
+    const float *p = &bvh.nodes[node * 8u];
+    out.insert(out.end(), { p[0], p[1], p[2], p[4], p[5], p[6] });
+  }
+}
+
+// -> false: no plan (trace every tile).  true: lens_tiles (hand-out order: rows from the outside in) and sky_tiles.
+static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<uint32_t> &lens_tiles, std::vector<uint32_t> &sky_tiles) {
+  bz_camera const &cam = desc.camera;
+  uint32_t const side = desc.tile_side;
+  if(std::getenv("BZ_B200_NO_PLAN") != nullptr) { return false; }                    // tuning runs only
+  if(lens->mode != BZ_MODE_CULLED || lens->outline.empty() || lens->tables.always_count != 0u || side * side > 1024u) { return false; }
+  double const m[3][3] = { { cam.right[0], cam.up[0], cam.forward[0] }, { cam.right[1], cam.up[1], cam.forward[1] }, { cam.right[2], cam.up[2], cam.forward[2] } };
+  double const det = m[0][0] * (m[1][1] * m[2][2] - m[1][2] * m[2][1]) - m[0][1] * (m[1][0] * m[2][2] - m[1][2] * m[2][0]) + m[0][2] * (m[1][0] * m[2][1] - m[1][1] * m[2][0]);
+  double scale = 0.0;
+  for(int r = 0; r < 3; ++r) { for(int c = 0; c < 3; ++c) { scale = std::max(scale, std::fabs(m[r][c])); } }
+  if(!(std::fabs(det) > 1e-9 * scale * scale * scale) || !(std::fabs((double)cam.half_w) > 0.0) || !(std::fabs((double)cam.half_h) > 0.0)) { return false; }
+  double inv[3][3];
+  for(int r = 0; r < 3; ++r) {
+    for(int c = 0; c < 3; ++c) {
+      int const r1 = (c + 1) % 3, r2 = (c + 2) % 3, c1 = (r + 1) % 3, c2 = (r + 2) % 3;
+      inv[r][c] = (m[r1][c1] * m[r2][c2] - m[r1][c2] * m[r2][c1]) / det;             // cofactor of m[c][r]
+    }
+  }
+  // the largest |origin|_1 of a ray of this camera; beyond origin_limit the wide segment is tested directly (no plan)
+  double origin = std::fabs((double)cam.eye[0]) + std::fabs((double)cam.eye[1]) + std::fabs((double)cam.eye[2]);
+  if(cam.ortho != 0u) {
+    for(int k = 0; k < 3; ++k) { origin += std::fabs((double)cam.half_w * cam.right[k]) + std::fabs((double)cam.half_h * cam.up[k]); }
+  }
+  if(!(origin * 1.001 <= (double)lens->tables.origin_limit)) { return false; }
+  double const grow = 4.0 * 3.0517578125e-05 * (origin + 2.0 * (double)lens->tables.extent);
+  // cells of side x side pixels of the WHOLE frame a projected box touches
+  uint32_t const cells_x = (cam.width + side - 1u) / side, cells_y = (cam.height + side - 1u) / side;
+  std::vector<uint8_t> touched((size_t)cells_x * cells_y, 0u);
+  for(size_t box = 0u; box < lens->outline.size(); box += 6u) {
+    const float *lo = &lens->outline[box], *hi = lo + 3;
+    double lo_u = 1e300, hi_u = -1e300, lo_v = 1e300, hi_v = -1e300;
+    int behind = 0;
+    for(int corner = 0; corner < 8; ++corner) {
+      double p[3];
+      for(int k = 0; k < 3; ++k) { p[k] = (((corner >> k) & 1) != 0 ? (double)hi[k] + grow : (double)lo[k] - grow) - (double)cam.eye[k]; }
+      double const x = inv[0][0] * p[0] + inv[0][1] * p[1] + inv[0][2] * p[2];
+      double const y = inv[1][0] * p[0] + inv[1][1] * p[1] + inv[1][2] * p[2];
+      double const z = inv[2][0] * p[0] + inv[2][1] * p[1] + inv[2][2] * p[2];
+      double a = x, b = y;
+      if(cam.ortho == 0u) {
+        if(!(z > 1e-6 * (std::fabs(x) + std::fabs(y) + std::fabs(z)))) { ++behind; continue; }
+        a = x / z; b = y / z;
+      }
+      double const fu = (a / (double)cam.half_w + 1.0) * 0.5 * (double)cam.width;    // csrc/bz_trace.cu: bzw_primary_ray
+      double const fv = (1.0 - b / (double)cam.half_h) * 0.5 * (double)cam.height;
+      if(!std::isfinite(fu) || !std::isfinite(fv)) { return false; }
+      lo_u = std::min(lo_u, fu); hi_u = std::max(hi_u, fu); lo_v = std::min(lo_v, fv); hi_v = std::max(hi_v, fv);
+    }
+    if(behind == 8) { continue; }                       // behind every ray
+    if(behind != 0) { return false; }                   // the box reaches beside or behind the eye
+    double const u0 = std::floor(lo_u) - 2.0, u1 = std::floor(hi_u) + 2.0, v0 = std::floor(lo_v) - 2.0, v1 = std::floor(hi_v) + 2.0;
+    if(u1 < 0.0 || v1 < 0.0 || u0 > (double)cam.width - 1.0 || v0 > (double)cam.height - 1.0) { continue; }      // off the image
+    uint32_t const cx0 = (uint32_t)std::max(u0, 0.0) / side, cx1 = (uint32_t)std::min(u1, (double)cam.width - 1.0) / side;
+    uint32_t const cy0 = (uint32_t)std::max(v0, 0.0) / side, cy1 = (uint32_t)std::min(v1, (double)cam.height - 1.0) / side;
+    for(uint32_t cy = cy0; cy <= cy1; ++cy) { std::memset(&touched[(size_t)cy * cells_x + cx0], 1, cx1 - cx0 + 1u); }
+  }
+  // tiles of the band: a tile's pixel columns are one cell column; its rows of the whole frame span one or more cell rows
+  auto frame_row = [&](uint32_t row) {                  // csrc/bz_trace.cu: bzw_frame_row
+    if(desc.stripe_rows == 0u) { return desc.row0 + row; }
+    uint32_t const stripe = row / desc.stripe_rows;
+    return (stripe * desc.stripe_ranks + desc.stripe_rank) * desc.stripe_rows + (row - stripe * desc.stripe_rows);
+  };
+  lens_tiles.clear();
+  sky_tiles.clear();
+  for(uint32_t turn = 0u; turn < desc.tiles_y; ++turn) {
+    uint32_t const ty = ((turn & 1u) == 0u) ? (turn >> 1) : (desc.tiles_y - 1u - (turn >> 1));     // rows from the outside in
+    uint32_t const row_a = ty * side, row_b = std::min(row_a + side, desc.rows) - 1u;
+    uint32_t const cy0 = std::min(frame_row(row_a), cam.height - 1u) / side, cy1 = std::min(frame_row(row_b), cam.height - 1u) / side;
+    for(uint32_t tx = 0u; tx < desc.tiles_x; ++tx) {
+      bool any = false;
+      for(uint32_t cy = cy0; cy <= cy1 && !any; ++cy) { any = touched[(size_t)cy * cells_x + tx] != 0u; }
+      (any ? lens_tiles : sky_tiles).push_back(ty * desc.tiles_x + tx);
+    }
+  }
+  return true;
+}
+
 static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
   BZ_CUDA(cudaSetDevice(lens->device));
   lens->timed = false;
+  lens->launches = 0u;
   if(desc.ray_count == 0u) { return BZ_OK; }
   BZ_CUDA(cudaMemsetAsync(lens->d_counter, 0, sizeof(unsigned long long), stream));
   desc.next_ray = lens->d_counter;
   desc.one = 1.0f;
   bool const brute = (lens->mode == BZ_MODE_BRUTE);
   int grid;
+  uint32_t sky_count = 0u;                // RENDER: tiles shaded by bz_sky_kernel (after the lens tiles in lens->d_tiles)
   if(brute) {
     uint64_t const threads = (uint64_t)bz_trace_threads();
     uint64_t const wanted = (desc.ray_count + threads - 1u) / threads;
@@ -264,6 +402,36 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
       desc.tiles_x = (desc.camera.width + side - 1u) / side;
       desc.tiles_y = (desc.rows + side - 1u) / side;
       desc.tile_count = (uint64_t)desc.tiles_x * desc.tiles_y;
+      if(desc.tile_count >= 0xffffffffull) { return bz_fail(BZ_ERR_INVALID, "job too large"); }
+      // the tiles that can meet the lens go to the trace kernel, the others to bz_sky_kernel; the plan of the last frame
+      // is kept (same camera, same band: nothing to do)
+      auto &plan = lens->plan;
+      bool const same = lens->mode == BZ_MODE_CULLED && plan.valid && std::memcmp(&plan.camera, &desc.camera, sizeof(bz_camera)) == 0 && plan.row0 == desc.row0 && plan.rows == desc.rows
+                     && plan.stripe_rows == desc.stripe_rows && plan.rank == desc.stripe_rank && plan.ranks == desc.stripe_ranks && plan.side == side;
+      if(!same) {
+        plan.valid = false;
+        std::vector<uint32_t> lens_tiles, sky_tiles;
+        if(bz_plan_tiles(lens, desc, lens_tiles, sky_tiles)) {
+          size_t const total = lens_tiles.size() + sky_tiles.size();
+          if(total > lens->tiles_capacity) {
+            if(lens->d_tiles != nullptr) { BZ_CUDA(cudaFree(lens->d_tiles)); lens->d_tiles = nullptr; lens->tiles_capacity = 0u; }
+            BZ_CUDA(cudaMalloc((void**)&lens->d_tiles, total * sizeof(uint32_t)));
+            lens->tiles_capacity = total;
+          }
+          lens_tiles.insert(lens_tiles.end(), sky_tiles.begin(), sky_tiles.end());
+          BZ_CUDA(cudaMemcpyAsync(lens->d_tiles, lens_tiles.data(), total * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));     // (pageable source: staged before the call returns)
+          plan.valid = true;
+          plan.camera = desc.camera;
+          plan.row0 = desc.row0; plan.rows = desc.rows; plan.stripe_rows = desc.stripe_rows; plan.rank = desc.stripe_rank; plan.ranks = desc.stripe_ranks; plan.side = side;
+          plan.sky_count = (uint32_t)sky_tiles.size();
+          plan.lens_count = (uint32_t)(total - sky_tiles.size());
+        }
+      }
+      if(plan.valid) {
+        desc.tile_list = lens->d_tiles;
+        desc.tile_count = plan.lens_count;
+        sky_count = plan.sky_count;
+      }
     }
     else {
       desc.tile_side = 0u;
@@ -278,11 +446,12 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
     grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * (uint64_t)std::max(perSm, 1), desc.tile_count);
   }
   BZ_CUDA(cudaEventRecord(lens->ev_begin, stream));
-  if(brute) { BZ_CUDA(bz_launch_trace(job, true, lens->tables, desc, grid, stream)); }
+  if(brute) { BZ_CUDA(bz_launch_trace(job, true, lens->tables, desc, grid, stream)); ++lens->launches; }
   else {
     bz_tables tables = lens->tables;
     if(lens->mode == BZ_MODE_LANES) { tables.packet_count = 0u; }
-    BZ_CUDA(bz_launch_warp_trace(job, tables, desc, grid, stream));
+    if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, lens->d_tiles + desc.tile_count, sky_count, stream)); ++lens->launches; }
+    if(grid != 0) { BZ_CUDA(bz_launch_warp_trace(job, tables, desc, grid, stream)); ++lens->launches; }
   }
   BZ_CUDA(cudaEventRecord(lens->ev_end, stream));
   lens->last_stream = stream;
@@ -329,6 +498,7 @@ static int bz_render_common(bz_lens *lens, const bz_camera *camera, const bz_sce
   int rc = bz_run(lens, BZ_JOB_RENDER, desc, stream);
   if(rc != BZ_OK) { return rc; }
   BZ_CUDA(bz_launch_resolve(lens->d_accum, d_rgba, pixels, spp, stream));
+  ++lens->launches;
   return BZ_OK;
 }
 
@@ -489,6 +659,12 @@ int bz_last_kernel_ms(bz_lens *lens, float *out_ms) {
   BZ_CUDA(cudaSetDevice(lens->device));
   BZ_CUDA(cudaEventSynchronize(lens->ev_end));
   BZ_CUDA(cudaEventElapsedTime(out_ms, lens->ev_begin, lens->ev_end));
+  return BZ_OK;
+}
+
+int bz_last_kernel_launches(const bz_lens *lens, uint32_t *out_count) {
+  if(lens == nullptr || out_count == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  *out_count = lens->launches;
   return BZ_OK;
 }
 

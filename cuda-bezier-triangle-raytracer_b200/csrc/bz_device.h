@@ -90,6 +90,9 @@ struct bz_job {
   uint32_t  tile_side, tile_rays, tiles_x, tiles_y;
   uint32_t  div_spp[2], div_strata[2], div_stripe[2];   // reciprocals for n / spp, n / strata, n / stripe_rows (bzw_div)
   float     two_over_w, two_over_h;                      // 2.0f / (float)width, 2.0f / (float)height
+  // RENDER: tiles whose rays may meet the lens, in the order they are handed out (tile_y * tiles_x + tile_x), or null = every
+  // tile of the band, rows from the outside in.  The other tiles of the band are shaded by bz_sky_kernel (csrc/bz_trace.cu).
+  const uint32_t *tile_list;
   uint64_t  tile_count;
   unsigned long long *next_ray;   // tile counter, zeroed before launch
   unsigned long long *stats;      // 9 counters in bz_stats order, accumulated; nullable

@@ -328,14 +328,31 @@ __device__ __forceinline__ void bzw_axis_bounds(const bzw_axis &a, const float *
 // ---- work distribution: tiles of the job from a global counter per CTA, packets of a tile from shared memory per warp ----
 // cta_work = tile << 32 | rays of the tile handed out so far.  The warp whose packet is the first one past the end of the
 // tile fetches the next tile (and takes its first packet); warps arriving in between wait for the tile number to change.
+// RENDER: tile = tile_y * tiles_x + tile_x.  With a tile list (the tiles that may meet the lens, csrc/bz_capi.cu) the order
+// is the list's; without one the rows are taken from the outside in (top, bottom, second, second to last, ...): the costliest
+// packets of a frame sit on the silhouette of the body (grazing rays meet many leaf boxes and walk per lane), the centre
+// rows are uniform -- ending on them keeps the tail of the persistent grid short, which matters for the short per-GPU
+// launches of a row-sharded frame.
+__device__ __forceinline__ unsigned long long bzw_fetch_tile(const bz_job &J) {
+  const unsigned long long next = atomicAdd(J.next_ray, 1ull);
+  if(next >= J.tile_count) { return (unsigned long long)BZ_END << 32; }
+  uint32_t tile = (uint32_t)next;
+  if(J.tile_list != nullptr) { tile = __ldg(J.tile_list + next); }
+  else if(J.tile_side != 0u) {
+    const uint32_t turn = tile / J.tiles_x, tile_x = tile - turn * J.tiles_x;
+    const uint32_t tile_y = ((turn & 1u) == 0u) ? (turn >> 1) : (J.tiles_y - 1u - (turn >> 1));
+    tile = tile_y * J.tiles_x + tile_x;
+  }
+  return (unsigned long long)tile << 32;
+}
+
 __device__ __forceinline__ unsigned long long bzw_take_packet(unsigned long long *cta_work, const bz_job &J) {
   for(;;) {
     const unsigned long long w = atomicAdd(cta_work, 32ull);
     const uint32_t tile = (uint32_t)(w >> 32), at = (uint32_t)w;
     if(tile == BZ_END || at < J.tile_rays) { return w; }
     if(at < J.tile_rays + 32u) {
-      const unsigned long long next = atomicAdd(J.next_ray, 1ull);
-      const unsigned long long fresh = ((next < J.tile_count) ? next : (unsigned long long)BZ_END) << 32;
+      const unsigned long long fresh = bzw_fetch_tile(J);
       atomicExch(cta_work, fresh | 32ull);
       return fresh;
     }
@@ -345,6 +362,13 @@ __device__ __forceinline__ unsigned long long bzw_take_packet(unsigned long long
 
 // n / d for a per-job divisor d: div = { ceil(2^32 / d) mod 2^32, d == 1 }, exact while n * d < 2^32 (the host checks)
 __device__ __forceinline__ uint32_t bzw_div(uint32_t n, const uint32_t div[2]) { return __umulhi(n, div[0]) + n * div[1]; }
+
+// RENDER: row of the whole frame behind a local row of the band (contiguous band from row0, or round-robin stripes)
+__device__ __forceinline__ uint32_t bzw_frame_row(const bz_job &J, uint32_t row) {
+  if(J.stripe_rows == 0u) { return J.row0 + row; }
+  const uint32_t stripe = bzw_div(row, J.div_stripe);
+  return (stripe * J.stripe_ranks + J.stripe_rank) * J.stripe_rows + (row - stripe * J.stripe_rows);
+}
 
 // the even bits of v, compacted: x of a Morton index (y = bzw_even_bits(v >> 1))
 __device__ __forceinline__ uint32_t bzw_even_bits(uint32_t v) {
@@ -371,10 +395,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
   for(int g = 0; g < BZ_GROUPS; ++g) { P.state[g * 32 + lane] = 0u; }
   if(lane == 0u) { P.qa_n = 0u; P.qb_n = 0u; }
   if(lane < BZ_NSTAT) { P.count[lane] = 0ull; }
-  if(threadIdx.x == 0u) {
-    const unsigned long long first = atomicAdd(J.next_ray, 1ull);
-    cta_work = ((first < J.tile_count) ? first : (unsigned long long)BZ_END) << 32;
-  }
+  if(threadIdx.x == 0u) { cta_work = bzw_fetch_tile(J); }
   __syncthreads();                           // the only CTA barrier of the kernel
   __syncwarp();
 
@@ -422,19 +443,12 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             if(JOB == BZ_JOB_RENDER) {
               // (divisions by per-job constants are multiplications by the host's reciprocals, bz_job::div_*)
               const uint32_t inside = bzw_div(at, J.div_spp), sample = at - inside * spp;   // pixel of the tile in Morton order, sample of the pixel
-              // tile rows are taken from the outside in (top, bottom, second, second to last, ...): the costliest packets of a
-              // frame sit on the silhouette of the body (grazing rays meet many leaf boxes and walk per lane), the centre rows
-              // are uniform -- ending on them keeps the tail of the persistent grid short, which matters for the short
-              // per-GPU launches of a row-sharded frame
-              const uint32_t turn = tile / J.tiles_x, tile_x = tile - turn * J.tiles_x;
-              const uint32_t tile_y = ((turn & 1u) == 0u) ? (turn >> 1) : (J.tiles_y - 1u - (turn >> 1));
+              const uint32_t tile_y = tile / J.tiles_x, tile_x = tile - tile_y * J.tiles_x;
               const uint32_t px = tile_x * J.tile_side + bzw_even_bits(inside), row = tile_y * J.tile_side + bzw_even_bits(inside >> 1);
               valid = valid && px < J.camera.width && row < J.rows;
               if(valid) {
-                const uint32_t stripe = bzw_div(row, J.div_stripe), sy = bzw_div(sample, J.div_strata);
-                const uint32_t py = (J.stripe_rows == 0u) ? J.row0 + row
-                                  : (stripe * J.stripe_ranks + J.stripe_rank) * J.stripe_rows + (row - stripe * J.stripe_rows);
-                bzw_primary_ray(J.camera, J.two_over_w, J.two_over_h, px, py, sample - sy * J.camera.strata, sy, s, d);
+                const uint32_t sy = bzw_div(sample, J.div_strata);
+                bzw_primary_ray(J.camera, J.two_over_w, J.two_over_h, px, bzw_frame_row(J, row), sample - sy * J.camera.strata, sy, s, d);
                 P.id_lo[slot] = row * J.camera.width + px;
               }
             }
@@ -915,4 +929,42 @@ cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta)
   cudaError_t e = bzw_configure();
   if(e != cudaSuccess) { return e; }
   return cudaOccupancyMaxActiveBlocksPerMultiprocessor(out_ctas_per_sm, bz_warp_trace_kernel<BZ_JOB_RENDER>, 32 * BZ_WARPS, bzw_shared_bytes());
+}
+
+// ---- sky tiles: the tiles of a RENDER job none of whose rays can meet the lens (csrc/bz_capi.cu: bz_plan_tiles) ----
+// Every refract() of such a ray is cNone (one call each, as in the bounce loop), so the pixel is the sum of the background
+// values of its samples: one CTA per tile, one thread per pixel, a plain store into the accumulator (no other kernel
+// writes these pixels).  The same ray generation and shading functions as the trace kernel, the same bits.
+__global__ void __launch_bounds__(1024) bz_sky_kernel(const bz_job J, const uint32_t *tiles) {
+  const uint32_t tile = __ldg(tiles + blockIdx.x);
+  const uint32_t tile_y = tile / J.tiles_x, tile_x = tile - tile_y * J.tiles_x;
+  const uint32_t in_y = threadIdx.x / J.tile_side, in_x = threadIdx.x - in_y * J.tile_side;
+  const uint32_t px = tile_x * J.tile_side + in_x, row = tile_y * J.tile_side + in_y;
+  const bool valid = px < J.camera.width && row < J.rows;
+  const uint32_t spp = J.camera.strata * J.camera.strata;
+  if(valid) {
+    const uint32_t py = bzw_frame_row(J, row);
+    uint32_t sum = 0u;
+#pragma unroll 1
+    for(uint32_t sy = 0u; sy < J.camera.strata; ++sy) {
+#pragma unroll 1
+      for(uint32_t sx = 0u; sx < J.camera.strata; ++sx) {
+        bzv3 s, d;
+        bzw_primary_ray(J.camera, J.two_over_w, J.two_over_h, px, py, sx, sy, s, d);
+        sum += bzw_shade_background(J.scene, s, d);
+      }
+    }
+    J.accum[row * J.camera.width + px] = sum;
+  }
+  const unsigned long long rays = (unsigned long long)__syncthreads_count(valid) * spp;
+  if(threadIdx.x == 0u && J.stats != nullptr && rays != 0ull) {
+    atomicAdd(J.stats + BZC_PRIMARY, rays);
+    atomicAdd(J.stats + BZC_CALLS, rays);
+  }
+}
+
+cudaError_t bz_launch_sky(const bz_job &desc, const uint32_t *d_tiles, uint32_t count, cudaStream_t stream) {
+  if(count == 0u) { return cudaSuccess; }
+  bz_sky_kernel<<<count, desc.tile_side * desc.tile_side, 0, stream>>>(desc, d_tiles);
+  return cudaGetLastError();
 }

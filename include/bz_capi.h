@@ -271,6 +271,10 @@ int  bz_fp32_peak_probe(int device, float *out_tflops, float *out_ms);
  * on this lens, measured with CUDA events on the stream the call used; synchronises that stream. */
 int  bz_last_kernel_ms(bz_lens *lens, float *out_ms);
 
+/* Kernels the most recent bz_render* / bz_refract_batch / bz_intersect_batch / bz_trace_to_target call on this lens launched
+ * (RENDER: bz_sky_kernel when the frame has tiles beside the lens, the trace kernel when it has tiles on it, the resolve). */
+int  bz_last_kernel_launches(const bz_lens *lens, uint32_t *out_count);
+
 #ifdef __cplusplus
 }
 #endif

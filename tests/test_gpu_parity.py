@@ -104,6 +104,42 @@ def test_render_pixel_exact_vs_reference(bz, oracle_built, name, w, h, strata, c
     assert ref_stats.entered > 100
 
 
+@pytest.mark.parametrize("label,cam_args,plans", [
+    ("oblique pinhole, skewed axes", dict(eye=(-9.0, 3.0, -2.0), forward=(0.9, -0.3, 0.2), right=(0.25, 1.0, 0.05), up=(-0.1, 0.1, 1.1), half_w=0.35), True),
+    ("lens in a corner of the frame", dict(eye=(-12.0, 2.5, 1.5), half_w=0.4), True),
+    ("lens off the frame", dict(eye=(-12.0, 0.0, 0.0), forward=(1.0, 1.5, 0.0), right=(-1.5, 1.0, 0.0), half_w=0.2), True),
+    ("orthographic, oblique", dict(eye=(-8.0, 0.5, 0.25), forward=(1.0, -0.05, 0.1), right=(0.05, 1.0, 0.0), up=(-0.1, 0.0, 1.0), half_w=2.5, ortho=True), True),
+    ("eye inside the body", dict(eye=(0.0, 0.1, 0.0), half_w=0.8), False),
+    ("lens behind the eye", dict(eye=(6.0, 0.0, 0.0), half_w=0.5), True),
+])
+def test_render_sky_tiles_pixel_exact(bz, oracle_built, label, cam_args, plans):
+    """tiles that cannot meet the lens are shaded by bz_sky_kernel: same pixels and counters as the reference and as the
+    arm without a tile plan (BZ_MODE_LANES), for cameras that exercise the projection of the hierarchy's boxes"""
+    import bzref
+    mesh, bezier, patches = common.ref_config("ellipsoid64x32")
+    w, h, strata = 192, 128, 2
+    rcam, rscene = bzref.make_camera(w, h, strata=strata, **cam_args), bzref.make_scene(bg_x=30.0, max_crossings=2)
+    ref_rgba, ref_stats, _ = bzref.RefLens(1.3, bezier).render(rcam, rscene, threads=8)
+    cam, scene = bz.make_camera(w, h, strata=strata, **cam_args), bz.make_scene(bg_x=30.0, max_crossings=2)
+    for mode in (bz.MODE_CULLED, bz.MODE_LANES):
+        lens = bz.BezierLens(1.3, patches).set_mode(mode)
+        for again in range(2):                                  # the second frame reuses the kept tile plan
+            rgba, stats = lens.render(cam, scene)
+            assert np.array_equal(rgba, ref_rgba), "%s: %d of %d pixels differ" % (label, int((rgba != ref_rgba).any(-1).sum()), w * h)
+            got, want = stats.as_dict(), ref_stats.as_dict()
+            for key in ("primary_rays", "refract_calls", "entered", "exited", "lost"):
+                assert got[key] == want[key], (label, key)
+        launches = lens.last_kernel_launches()
+        if mode == bz.MODE_CULLED and plans:
+            assert launches == (3 if ref_stats.entered > 0 else 2), label        # sky + trace + resolve; no trace when nothing can meet the lens
+        else:
+            assert launches == 2, label
+        # a band of the frame and a moved camera make a new plan
+        if mode == bz.MODE_CULLED:
+            band, _ = lens.render(cam, scene, 37, 101)
+            assert np.array_equal(band, ref_rgba[37:101]), label
+
+
 def test_render_bands_and_stripes_compose(bz, oracle_built):
     """row bands and round-robin stripes reproduce the full frame byte for byte (multi-GPU sharding, one device)"""
     import torch
