@@ -294,7 +294,7 @@ def main_ours(args, name):
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         achieved_tf = flop / (k_ms * 1e-3) / 1e12
         roofline = {
-            "bound": "fp32_alu", "kernel": "bz_warp_trace_kernel<RENDER> (packet walk)", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+            "bound": "fp32_alu", "kernel": "bz_warp_trace_kernel<RENDER> (packet walk; kernel_ms also holds bz_sky_kernel, 0.5 of 18.6 ms on cfg4)", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
             "frac": achieved_tf / peak_tf, "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_source,
             "frac_of_no_fma_ceiling": achieved_tf / (peak_tf / 2.0),
             "no_fma_note": "the parity build has no FMA contraction (bit-exact with the reference's x86 build): one flop per lane and instruction, half the probe's peak",
