@@ -6,7 +6,7 @@
 
 One step = one whole frame of the workload (default: cfg4, makeEllipsoid(181,91,(1,4,2)) -> 98 826 patches,
 3840x2160, 16 rays/pixel = 132 710 400 primary rays), image rows dealt to the N ranks in round-robin stripes
-of 16 rows, tables replicated, one NCCL all-gather of the rendered stripes per step when N > 1 (strong
+of 8 rows, tables replicated, one NCCL all-gather of the rendered stripes per step when N > 1 (strong
 scaling: the frame is fixed).  `value` = primary rays of the frame / device time per step, max over ranks.
 `e2e` goes through the host-buffer C-ABI call (bz_render_host, N = 1) or render + gather + device->pinned-host
 copy of the frame (N > 1), every step.  `--impl reference` times the reference's own CPU code

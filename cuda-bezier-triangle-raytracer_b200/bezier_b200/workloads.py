@@ -27,7 +27,7 @@ ILLUMINATION = {
                                     ri=1.3, max_crossings=2),
 }
 HEADLINE = "cfg4_freeform181x91_4k_16spp"
-STRIPE_ROWS = 16
+STRIPE_ROWS = 8       # one tile row of the 4K frame; 270 stripes: a stripe and its mirror image never fall on the same rank at N = 8
 
 
 def build_mesh(mesh_class, recipe):

@@ -309,7 +309,7 @@ static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<u
   double const grow = 4.0 * 3.0517578125e-05 * (origin + 2.0 * (double)lens->tables.extent);
   // cells of side x side pixels of the WHOLE frame a projected box touches
   uint32_t const cells_x = (cam.width + side - 1u) / side, cells_y = (cam.height + side - 1u) / side;
-  std::vector<uint8_t> touched((size_t)cells_x * cells_y, 0u);
+  std::vector<uint16_t> touched((size_t)cells_x * cells_y, 0u);     // how many outline boxes project onto the cell (saturating)
   for(size_t box = 0u; box < lens->outline.size(); box += 6u) {
     const float *lo = &lens->outline[box], *hi = lo + 3;
     double lo_u = 1e300, hi_u = -1e300, lo_v = 1e300, hi_v = -1e300;
@@ -336,7 +336,10 @@ static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<u
     if(u1 < 0.0 || v1 < 0.0 || u0 > (double)cam.width - 1.0 || v0 > (double)cam.height - 1.0) { continue; }      // off the image
     uint32_t const cx0 = (uint32_t)std::max(u0, 0.0) / side, cx1 = (uint32_t)std::min(u1, (double)cam.width - 1.0) / side;
     uint32_t const cy0 = (uint32_t)std::max(v0, 0.0) / side, cy1 = (uint32_t)std::min(v1, (double)cam.height - 1.0) / side;
-    for(uint32_t cy = cy0; cy <= cy1; ++cy) { std::memset(&touched[(size_t)cy * cells_x + cx0], 1, cx1 - cx0 + 1u); }
+    for(uint32_t cy = cy0; cy <= cy1; ++cy) {
+      uint16_t *cell = &touched[(size_t)cy * cells_x];
+      for(uint32_t cx = cx0; cx <= cx1; ++cx) { cell[cx] = (uint16_t)std::min<uint32_t>(cell[cx] + 1u, 0xffffu); }
+    }
   }
   // tiles of the band: a tile's pixel columns are one cell column; its rows of the whole frame span one or more cell rows
   auto frame_row = [&](uint32_t row) {                  // csrc/bz_trace.cu: bzw_frame_row
@@ -346,15 +349,27 @@ static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<u
   };
   lens_tiles.clear();
   sky_tiles.clear();
+  std::vector<uint32_t> weight;                         // per lens tile: outline boxes that project onto it
   for(uint32_t turn = 0u; turn < desc.tiles_y; ++turn) {
     uint32_t const ty = ((turn & 1u) == 0u) ? (turn >> 1) : (desc.tiles_y - 1u - (turn >> 1));     // rows from the outside in
     uint32_t const row_a = ty * side, row_b = std::min(row_a + side, desc.rows) - 1u;
     uint32_t const cy0 = std::min(frame_row(row_a), cam.height - 1u) / side, cy1 = std::min(frame_row(row_b), cam.height - 1u) / side;
     for(uint32_t tx = 0u; tx < desc.tiles_x; ++tx) {
-      bool any = false;
-      for(uint32_t cy = cy0; cy <= cy1 && !any; ++cy) { any = touched[(size_t)cy * cells_x + tx] != 0u; }
-      (any ? lens_tiles : sky_tiles).push_back(ty * desc.tiles_x + tx);
+      uint32_t boxes = 0u;
+      for(uint32_t cy = cy0; cy <= cy1; ++cy) { boxes = std::max<uint32_t>(boxes, touched[(size_t)cy * cells_x + tx]); }
+      if(boxes != 0u) { lens_tiles.push_back(ty * desc.tiles_x + tx); weight.push_back(boxes); }
+      else { sky_tiles.push_back(ty * desc.tiles_x + tx); }
     }
+  }
+  // the tiles many boxes project onto (silhouette of the body: thick projections, grazing rays, the costliest packets of the
+  // frame) are handed out first, so the persistent grid ends on cheap tiles; within a weight the outside-in order stays
+  if(std::getenv("BZ_B200_NO_SORT") == nullptr) {                                     // tuning runs only
+    std::vector<uint32_t> index(lens_tiles.size());
+    for(uint32_t i = 0u; i < index.size(); ++i) { index[i] = i; }
+    std::stable_sort(index.begin(), index.end(), [&](uint32_t a, uint32_t b) { return weight[a] > weight[b]; });
+    std::vector<uint32_t> sorted(lens_tiles.size());
+    for(uint32_t i = 0u; i < index.size(); ++i) { sorted[i] = lens_tiles[index[i]]; }
+    lens_tiles.swap(sorted);
   }
   return true;
 }
