@@ -51,7 +51,7 @@
 #define BZ_QA_CAP    256
 #endif
 #ifndef BZ_CAND_CAP
-#define BZ_CAND_CAP  96      // leaves a packet may collect before it is declared incoherent
+#define BZ_CAND_CAP  160     // leaves a packet may collect before it is declared incoherent
 #endif
 #define BZ_STACK_CAP 96
 #define BZ_QB_CAP    160
