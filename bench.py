@@ -372,6 +372,7 @@ def main_illumination(args, name):
     ms = begin.elapsed_time(end) / args.steps
     clocks = sampler.stop(wall0, wall1)
     work = dict(zip(bz.STAT_NAMES, [int(x) // args.steps for x in stats.tolist()]))
+    launches = lens.last_kernel_launches()             # emit, pass, count, scan, scatter, trace
     host_bins = torch.zeros((target.bins_v, target.bins_u), dtype=torch.int32).pin_memory().numpy().view("uint32")
     lens.illuminate(emitter, target, spec["max_crossings"], bins=host_bins)              # warm-up: the call's device scratch is allocated on first use
     t0 = time.perf_counter()
@@ -387,7 +388,7 @@ def main_illumination(args, name):
                    "max_crossings": spec["max_crossings"], "l2": "flushed between steps (256 MiB fill)"},
         "e2e": {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(host_bins.nbytes + 140), "d2h_bytes_per_step": int(host_bins.nbytes),
                 "ms_per_step": e2e_s * 1e3, "call": "bz_illuminate_host"},
-        "gpu_launches": 6 * args.steps, "clocks": clocks, "work_per_step": work, "landed": int(bins.sum().item()),
+        "gpu_launches": launches * args.steps, "clocks": clocks, "work_per_step": work, "landed": int(bins.sum().item()),
     }))
 
 

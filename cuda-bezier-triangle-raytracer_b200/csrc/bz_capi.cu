@@ -23,12 +23,13 @@ cudaError_t bz_launch_assemble(const uint8_t *bands, uint32_t band_rows, uint32_
 cudaError_t bz_launch_fma_probe(float *sink, uint32_t iters, int grid, cudaStream_t stream);
 int bz_trace_threads(void);
 cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream);
+cudaError_t bz_launch_pass(const bz_tables &tables, const bz_job &desc, const float *start, const float *dir, uint32_t *patch, uint64_t count, cudaStream_t stream);
 cudaError_t bz_launch_sky(const bz_job &desc, const uint32_t *d_tiles, uint32_t count, cudaStream_t stream);
 cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta);
 cudaError_t bz_launch_emit(const bz_emitter &em, const bz_belts &belts, uint64_t first, uint64_t count, float *start, float *dir, uint32_t *patch,
                            cudaStream_t stream);
-cudaError_t bz_launch_group_by_patch(const uint32_t *patch, uint64_t count, uint32_t patches, uint32_t *counts, const float *start, const float *dir,
-                                     float *out_start, float *out_dir, int sm_count, cudaStream_t stream);
+cudaError_t bz_launch_group_by_patch(const uint32_t *patch, uint64_t count, uint32_t patches, uint32_t ways, uint32_t *counts,
+                                     const float *start, const float *dir, float *out_start, float *out_dir, int sm_count, cudaStream_t stream);
 
 static thread_local std::string gError;
 
@@ -779,13 +780,13 @@ int bz_emit_rays(const bz_emitter *emitter, uint64_t first, uint64_t count, floa
   return BZ_OK;
 }
 
-int bz_trace_to_target(bz_lens *lens, const float *d_start, const float *d_dir, uint64_t n, const bz_target *target, uint32_t max_crossings,
-                       uint32_t *d_bins, uint32_t *d_landing, bz_stats *d_stats, void *stream) {
+// the BZ_JOB_TARGET description of a call (everything but the launch)
+static int bz_target_job(bz_lens *lens, const float *d_start, const float *d_dir, uint64_t n, const bz_target *target, uint32_t max_crossings,
+                         uint32_t *d_bins, uint32_t *d_landing, bz_stats *d_stats, bz_job &desc) {
   if(lens == nullptr || target == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
   if(target->bins_u == 0u || target->bins_v == 0u || (uint64_t)target->bins_u * target->bins_v >= BZ_LAND_MISSED) { return bz_fail(BZ_ERR_INVALID, "bad bin counts"); }
   if(n != 0u && (d_start == nullptr || d_dir == nullptr || d_bins == nullptr)) { return bz_fail(BZ_ERR_INVALID, "null buffer"); }
   if(lens->mode == BZ_MODE_BRUTE) { return bz_fail(BZ_ERR_INVALID, "the illumination mode runs on the culled kernel only"); }
-  bz_job desc;
   std::memset(&desc, 0, sizeof(desc));
   desc.in_start = d_start; desc.in_dir = d_dir;
   desc.target = *target;
@@ -801,6 +802,14 @@ int bz_trace_to_target(bz_lens *lens, const float *d_start, const float *d_dir, 
   desc.scene.max_crossings = max_crossings;
   desc.ray_count = n;
   desc.stats = (unsigned long long*)d_stats;
+  return BZ_OK;
+}
+
+int bz_trace_to_target(bz_lens *lens, const float *d_start, const float *d_dir, uint64_t n, const bz_target *target, uint32_t max_crossings,
+                       uint32_t *d_bins, uint32_t *d_landing, bz_stats *d_stats, void *stream) {
+  bz_job desc;
+  int rc = bz_target_job(lens, d_start, d_dir, n, target, max_crossings, d_bins, d_landing, d_stats, desc);
+  if(rc != BZ_OK) { return rc; }
   return bz_run(lens, BZ_JOB_TARGET, desc, (cudaStream_t)stream);
 }
 
@@ -815,7 +824,9 @@ int bz_illuminate(bz_lens *lens, const bz_emitter *emitter, const bz_target *tar
   if(rc != BZ_OK) { return rc; }
   BZ_CUDA(cudaSetDevice(lens->device));
   // scratch of the lens handle: emitted rays, patch keys, group offsets, grouped rays
-  size_t const keys = ((size_t)rays * 4u + 255u) / 256u * 256u, counts = ((size_t)table.patches * 4u + 255u) / 256u * 256u;
+  uint32_t const ways = 64u;              // counters per patch (csrc/bz_illum.cu)
+  size_t const groups = (size_t)table.patches * ways;
+  size_t const keys = ((size_t)rays * 4u + 255u) / 256u * 256u, counts = ((size_t)(groups + 1u) * 4u + 255u) / 256u * 256u;
   if(lens->d_illum == nullptr || lens->illum_bytes < (size_t)rays * 48u + keys + counts) {
     if(lens->d_illum != nullptr) { BZ_CUDA(cudaFree(lens->d_illum)); lens->d_illum = nullptr; lens->illum_bytes = 0u; }
     BZ_CUDA(cudaMalloc(&lens->d_illum, (size_t)rays * 48u + keys + counts));
@@ -824,10 +835,18 @@ int bz_illuminate(bz_lens *lens, const bz_emitter *emitter, const bz_target *tar
   cudaStream_t const st = (cudaStream_t)stream;
   float *start = (float*)lens->d_illum, *dir = start + rays * 3u, *sorted_start = dir + rays * 3u, *sorted_dir = sorted_start + rays * 3u;
   uint32_t *patch = (uint32_t*)(sorted_dir + rays * 3u), *group = (uint32_t*)((char*)patch + keys);
+  bz_job desc;
+  rc = bz_target_job(lens, sorted_start, sorted_dir, rays, target, max_crossings, d_bins, nullptr, d_stats, desc);
+  if(rc != BZ_OK) { return rc; }
   BZ_CUDA(bz_launch_emit(*emitter, table, 0u, rays, start, dir, patch, st));
+  // rays that pass beside the lens land on the target at once; the others are grouped by patch and traced
+  BZ_CUDA(bz_launch_pass(lens->tables, desc, start, dir, patch, rays, st));
   BZ_CUDA(cudaMemsetAsync(group, 0, counts, st));
-  BZ_CUDA(bz_launch_group_by_patch(patch, rays, table.patches, group, start, dir, sorted_start, sorted_dir, lens->sm_count, st));
-  return bz_trace_to_target(lens, sorted_start, sorted_dir, rays, target, max_crossings, d_bins, nullptr, d_stats, stream);
+  BZ_CUDA(bz_launch_group_by_patch(patch, rays, table.patches, ways, group, start, dir, sorted_start, sorted_dir, lens->sm_count, st));
+  desc.ray_count_dev = group + groups;
+  rc = bz_run(lens, BZ_JOB_TARGET, desc, st);
+  lens->launches += 5u;                   // emit, pass, count, scan, scatter
+  return rc;
 }
 
 int bz_illuminate_host(bz_lens *lens, const bz_emitter *emitter, const bz_target *target, uint32_t max_crossings,

@@ -82,6 +82,7 @@ struct bz_job {
   uint32_t *out_landing;       // nullable: per ray the bin, BZ_LAND_LOST or BZ_LAND_MISSED
   // all
   uint64_t  ray_count;       // primary rays of this call
+  const uint32_t *ray_count_dev;   // BZ_JOB_TARGET, nullable: the rays actually there (<= ray_count), known on the device only
   float     one;             // 1.0f, as a run-time value (csrc/bz_trace.cu: packed sums)
   // work distribution: the job is cut into tiles handed to CTAs; RENDER: square blocks of tile_side x tile_side pixels
   // (tile_side a power of two, pixels of a tile in Morton order, tile_rays = tile_side^2 * spp); batch jobs: tile_rays
@@ -97,6 +98,8 @@ struct bz_job {
   unsigned long long *next_ray;   // tile counter, zeroed before launch
   unsigned long long *stats;      // 9 counters in bz_stats order, accumulated; nullable
 };
+
+#define BZ_RAY_PASSED 0xffffffffu     // illumination mode: patch key of an emitter ray that passed beside the lens (bz_pass_kernel)
 
 // UniformHemisphere belt table (reference/hostUtil.cpp:8-13), passed to the emission kernel by value
 #define BZ_MAX_BELTS 128

@@ -59,12 +59,21 @@ __global__ void bz_emit_kernel(const bz_emitter em, const bz_belts belts, uint64
 }
 
 // ---- counting sort by hemisphere patch ----
-__global__ void bz_patch_count_kernel(const uint32_t *patch, uint64_t count, uint32_t *counts) {
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for(uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) { atomicAdd(counts + patch[i], 1u); }
+// README.md:176-186: one ray vector per patch, so that the rays traced together have similar directions.  Every patch has
+// `ways` counters (key = patch * ways + ray mod ways; the order inside a patch does not matter): 4.2 M atomics on 660
+// addresses took 0.46 ms, on 660 x 64 they take 0.05 ms.  Hand-written, no Thrust.
+__device__ __forceinline__ uint32_t bz_group_key(const uint32_t *patch, uint64_t i, uint32_t ways) {
+  return patch[i] * ways + (uint32_t)(i % ways);
 }
 
-// one CTA: counts[0..n) -> exclusive prefix sums in place (n is a few thousand at most)
+__global__ void bz_patch_count_kernel(const uint32_t *patch, uint64_t count, uint32_t ways, uint32_t *counts) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for(uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+    if(patch[i] != BZ_RAY_PASSED) { atomicAdd(counts + bz_group_key(patch, i, ways), 1u); }      // (bz_pass_kernel dealt with the others)
+  }
+}
+
+// one CTA: counts[0..n) -> exclusive prefix sums in place, counts[n] = their total
 __global__ void bz_patch_scan_kernel(uint32_t *counts, uint32_t n) {
   __shared__ uint32_t partial[1024];
   const uint32_t per = (n + blockDim.x - 1u) / blockDim.x;
@@ -80,13 +89,15 @@ __global__ void bz_patch_scan_kernel(uint32_t *counts, uint32_t n) {
   __syncthreads();
   uint32_t run = partial[threadIdx.x];
   for(uint32_t i = begin; i < end; ++i) { const uint32_t v = counts[i]; counts[i] = run; run += v; }
+  if(threadIdx.x == blockDim.x - 1u) { counts[n] = run; }
 }
 
-__global__ void bz_patch_scatter_kernel(const uint32_t *patch, uint64_t count, uint32_t *cursor, const float *start, const float *dir,
-                                        float *out_start, float *out_dir) {
+__global__ void bz_patch_scatter_kernel(const uint32_t *patch, uint64_t count, uint32_t ways, uint32_t *cursor,
+                                        const float *start, const float *dir, float *out_start, float *out_dir) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for(uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
-    const uint64_t at = atomicAdd(cursor + patch[i], 1u);
+    if(patch[i] == BZ_RAY_PASSED) { continue; }
+    const uint64_t at = atomicAdd(cursor + bz_group_key(patch, i, ways), 1u);
     out_start[at * 3u] = start[i * 3u]; out_start[at * 3u + 1u] = start[i * 3u + 1u]; out_start[at * 3u + 2u] = start[i * 3u + 2u];
     out_dir[at * 3u] = dir[i * 3u]; out_dir[at * 3u + 1u] = dir[i * 3u + 1u]; out_dir[at * 3u + 2u] = dir[i * 3u + 2u];
   }
@@ -99,13 +110,14 @@ cudaError_t bz_launch_emit(const bz_emitter &em, const bz_belts &belts, uint64_t
   return cudaGetLastError();
 }
 
-// rays grouped by patch: counts must hold belts.patches zeroed counters; they end up as the end offsets of the groups
-cudaError_t bz_launch_group_by_patch(const uint32_t *patch, uint64_t count, uint32_t patches, uint32_t *counts, const float *start, const float *dir,
-                                     float *out_start, float *out_dir, int sm_count, cudaStream_t stream) {
+// rays grouped by patch: counts must hold patches * ways + 1 zeroed counters; they end up as the end offsets of the groups,
+// the last one as the number of rays grouped (rays with the key BZ_RAY_PASSED are left out)
+cudaError_t bz_launch_group_by_patch(const uint32_t *patch, uint64_t count, uint32_t patches, uint32_t ways, uint32_t *counts,
+                                     const float *start, const float *dir, float *out_start, float *out_dir, int sm_count, cudaStream_t stream) {
   if(count == 0u) { return cudaSuccess; }
   const unsigned grid = (unsigned)sm_count * 8u;
-  bz_patch_count_kernel<<<grid, 256, 0, stream>>>(patch, count, counts);
-  bz_patch_scan_kernel<<<1, 1024, 0, stream>>>(counts, patches);
-  bz_patch_scatter_kernel<<<grid, 256, 0, stream>>>(patch, count, counts, start, dir, out_start, out_dir);
+  bz_patch_count_kernel<<<grid, 256, 0, stream>>>(patch, count, ways, counts);
+  bz_patch_scan_kernel<<<1, 1024, 0, stream>>>(counts, patches * ways);
+  bz_patch_scatter_kernel<<<grid, 256, 0, stream>>>(patch, count, ways, counts, start, dir, out_start, out_dir);
   return cudaGetLastError();
 }

@@ -389,6 +389,8 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
   const uint32_t spp = J.camera.strata * J.camera.strata;
   const uint32_t direct_end = T.always_first + T.always_count;
   bool exhausted = false;                    // warp-uniform: the global ray counter has run past the end
+  // batch jobs: rays of the call (BZ_JOB_TARGET after bz_pass_kernel: the count is known on the device only)
+  const unsigned long long ray_count = (JOB == BZ_JOB_TARGET && J.ray_count_dev != nullptr) ? (unsigned long long)__ldg(J.ray_count_dev) : J.ray_count;
   uint32_t tally = 0u, tally_turns = 0u;     // per lane: packed event counters of the resolve step; warp-uniform: turns since their last fold
 
 #pragma unroll
@@ -454,7 +456,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             }
             else {
               const unsigned long long id = (unsigned long long)tile * J.tile_rays + at;
-              valid = valid && id < J.ray_count;
+              valid = valid && id < ray_count;
               if(valid) {
                 s = bz_v(J.in_start[id * 3u], J.in_start[id * 3u + 1u], J.in_start[id * 3u + 2u]);
                 d = bz_v(J.in_dir[id * 3u], J.in_dir[id * 3u + 1u], J.in_dir[id * 3u + 2u]);
@@ -966,5 +968,53 @@ __global__ void __launch_bounds__(1024) bz_sky_kernel(const bz_job J, const uint
 cudaError_t bz_launch_sky(const bz_job &desc, const uint32_t *d_tiles, uint32_t count, cudaStream_t stream) {
   if(count == 0u) { return cudaSuccess; }
   bz_sky_kernel<<<count, desc.tile_side * desc.tile_side, 0, stream>>>(desc, d_tiles);
+  return cudaGetLastError();
+}
+
+// ---- illumination mode: emitter rays that pass beside the lens ----
+// Most rays of a hemisphere emitter never come near the lens.  A ray that misses the root box of the cull hierarchy grown
+// by TWICE the lane walk's slack fails stage A of every patch (the hierarchy's guarantee, with a share to spare for the
+// rounding of this test), so its only refract() is cNone: it lands on the target here, and its patch key becomes
+// BZ_RAY_PASSED so that the grouping (csrc/bz_illum.cu) leaves it out of the rays the trace kernel gets.
+__global__ void __launch_bounds__(256) bz_pass_kernel(const bz_tables T, const bz_job J, const float *start, const float *dir, uint32_t *patch, uint64_t count) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool passed = false;
+  if(i < count) {
+    const bzv3 s = bz_v(start[i * 3u], start[i * 3u + 1u], start[i * 3u + 2u]);
+    const bzv3 d = bz_v(dir[i * 3u], dir[i * 3u + 1u], dir[i * 3u + 2u]);
+    const float l1 = fabsf(s.x) + fabsf(s.y) + fabsf(s.z);
+    // records outside the hierarchy are tested by every ray (always segment) or by rays from far away (wide segment)
+    const bool direct = (T.always_count != 0u) || !(l1 <= T.origin_limit);
+    bool misses = (T.node_count == 0u);
+    if(T.node_count != 0u) {
+      const float4 lo = __ldg(T.nodes), hi = __ldg(T.nodes + 1);
+      const float slack = 2.0f * 3.0517578125e-05f * (l1 + 2.0f * T.extent);
+      const float ix = (fabsf(d.x) > 1e-20f) ? 1.0f / d.x : copysignf(1e20f, d.x);
+      const float iy = (fabsf(d.y) > 1e-20f) ? 1.0f / d.y : copysignf(1e20f, d.y);
+      const float iz = (fabsf(d.z) > 1e-20f) ? 1.0f / d.z : copysignf(1e20f, d.z);
+      const float x0 = (lo.x - slack - s.x) * ix, x1 = (hi.x + slack - s.x) * ix;
+      const float y0 = (lo.y - slack - s.y) * iy, y1 = (hi.y + slack - s.y) * iy;
+      const float z0 = (lo.z - slack - s.z) * iz, z1 = (hi.z + slack - s.z) * iz;
+      const float tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+      const float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+      misses = !(tnear <= tfar * 1.000001f);      // (NaN: not a miss)
+    }
+    passed = misses && !direct;
+    if(passed) {
+      const uint32_t value = bzw_land_on_target(J, s, d);
+      if(value < BZ_LAND_MISSED) { atomicAdd(J.bins + value, 1u); }
+      patch[i] = BZ_RAY_PASSED;
+    }
+  }
+  const unsigned long long rays = (unsigned long long)__syncthreads_count(passed);
+  if(threadIdx.x == 0u && J.stats != nullptr && rays != 0ull) {
+    atomicAdd(J.stats + BZC_PRIMARY, rays);
+    atomicAdd(J.stats + BZC_CALLS, rays);
+  }
+}
+
+cudaError_t bz_launch_pass(const bz_tables &tables, const bz_job &desc, const float *start, const float *dir, uint32_t *patch, uint64_t count, cudaStream_t stream) {
+  if(count == 0u) { return cudaSuccess; }
+  bz_pass_kernel<<<(unsigned)((count + 255u) / 256u), 256, 0, stream>>>(tables, desc, start, dir, patch, count);
   return cudaGetLastError();
 }
