@@ -69,6 +69,8 @@ struct bz_lens {
   } plan;
   uint32_t  *d_tiles;
   size_t     tiles_capacity;
+  cudaEvent_t ev_plan;                // the upload of d_tiles (a call on another stream waits for it)
+  cudaStream_t plan_stream;
   uint32_t   launches;                // kernels of the most recent call
 };
 
@@ -109,6 +111,7 @@ int bz_lens_destroy(bz_lens *lens) {
   cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_pairs); cudaFree(lens->d_nodes); cudaFree(lens->d_packet);
   cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch); cudaFree(lens->d_illum); cudaFree(lens->d_tiles);
   if(lens->ev_begin) { cudaEventDestroy(lens->ev_begin); }
+  if(lens->ev_plan) { cudaEventDestroy(lens->ev_plan); }
   if(lens->ev_end) { cudaEventDestroy(lens->ev_end); }
   delete lens;
   return BZ_OK;
@@ -188,6 +191,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   if(e == cudaSuccess) { e = upload(bvh.packet_nodes, &lens->d_packet); }
   if(e == cudaSuccess) { e = cudaMalloc((void**)&lens->d_counter, 64u); }
   if(e == cudaSuccess) { e = cudaEventCreate(&lens->ev_begin); }
+  if(e == cudaSuccess) { e = cudaEventCreateWithFlags(&lens->ev_plan, cudaEventDisableTiming); }
   if(e == cudaSuccess) { e = cudaEventCreate(&lens->ev_end); }
   if(e != cudaSuccess) {
     std::string text = cudaGetErrorString(e);
@@ -436,6 +440,8 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
           }
           lens_tiles.insert(lens_tiles.end(), sky_tiles.begin(), sky_tiles.end());
           BZ_CUDA(cudaMemcpyAsync(lens->d_tiles, lens_tiles.data(), total * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));     // (pageable source: staged before the call returns)
+          BZ_CUDA(cudaEventRecord(lens->ev_plan, stream));
+          lens->plan_stream = stream;
           plan.valid = true;
           plan.camera = desc.camera;
           plan.row0 = desc.row0; plan.rows = desc.rows; plan.stripe_rows = desc.stripe_rows; plan.rank = desc.stripe_rank; plan.ranks = desc.stripe_ranks; plan.side = side;
@@ -444,6 +450,7 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
         }
       }
       if(plan.valid) {
+        if(stream != lens->plan_stream) { BZ_CUDA(cudaStreamWaitEvent(stream, lens->ev_plan, 0)); }
         desc.tile_list = lens->d_tiles;
         desc.tile_count = plan.lens_count;
         sky_count = plan.sky_count;
