@@ -186,7 +186,11 @@ int  bz_intersect_batch_host(bz_lens *lens, const float *h_start, const float *h
 int  bz_generate_rays(const bz_camera *camera, uint32_t row0, uint32_t row1, float *d_start, float *d_dir, void *stream);
 
 /* K1+K2+K3: render rows [row0,row1) into d_rgba ((row1-row0) x width x 4 bytes, row-major,
- * R=G=B=value, A=255).  d_stats (nullable) is ACCUMULATED into (device memory, caller zeroes). */
+ * R=G=B=value, A=255).  d_stats (nullable) is ACCUMULATED into (device memory, caller zeroes).
+ * In BZ_MODE_CULLED the call plans the frame: tiles of pixels onto which no box of the cull hierarchy projects
+ * are shaded by a separate kernel (their rays count in primary_rays and refract_calls, they do no walk), the
+ * other tiles are traced.  The plan of the last frame is kept in the lens handle, so the calls on one handle
+ * must not overlap in time (they share the handle's accumulator and work counter anyway). */
 int  bz_render(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
                uint8_t *d_rgba, bz_stats *d_stats, void *stream);
 int  bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
