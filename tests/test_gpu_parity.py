@@ -140,6 +140,38 @@ def test_render_sky_tiles_pixel_exact(bz, oracle_built, label, cam_args, plans):
             assert np.array_equal(band, ref_rgba[37:101]), label
 
 
+def test_tile_plan_against_the_arm_without_one_random_cameras(bz, oracle_built):
+    """60 random cameras (pinhole and orthographic, any orientation, skewed axes, near and far, lens partly or wholly off the
+    frame): the planned frame (sky tiles + lens tiles) equals the frame of BZ_MODE_LANES, which traces every tile"""
+    mesh, bezier, patches = common.ref_config("sphere32x16")
+    planned, plain = bz.BezierLens(1.3, patches), bz.BezierLens(1.3, patches).set_mode(bz.MODE_LANES)
+    rng = np.random.default_rng(2024)
+    scene = bz.make_scene(bg_x=40.0, max_crossings=2)
+    with_sky = 0
+    for case in range(60):
+        eye = rng.normal(size=3)
+        eye = eye / np.linalg.norm(eye) * rng.uniform(1.3, 30.0)
+        aim = rng.uniform(-1.5, 1.5, size=3) * (0.0 if case % 3 == 0 else 1.0)           # every third camera looks at the centre
+        forward = aim - eye
+        forward /= np.linalg.norm(forward)
+        helper = np.array([0.0, 0.0, 1.0]) if abs(forward[2]) < 0.9 else np.array([0.0, 1.0, 0.0])
+        right = np.cross(forward, helper)
+        right /= np.linalg.norm(right)
+        up = np.cross(right, forward)
+        right = right * rng.uniform(0.5, 2.0) + forward * rng.uniform(-0.2, 0.2)            # skewed, unnormalised axes
+        up = up * rng.uniform(0.5, 2.0) + right * rng.uniform(-0.2, 0.2)
+        ortho = case % 4 == 3
+        half_w = rng.uniform(0.5, 3.0) if ortho else rng.uniform(0.05, 1.5)
+        cam = bz.make_camera(160, 96, strata=1 + case % 3, eye=tuple(eye), forward=tuple(forward), right=tuple(right), up=tuple(up), half_w=float(half_w), ortho=ortho)
+        a, sa = planned.render(cam, scene)
+        with_sky += planned.last_kernel_launches() == 3 or (planned.last_kernel_launches() == 2 and sa.packet_walks == 0 and sa.lane_walk_calls == 0)
+        b, sb = plain.render(cam, scene)
+        assert np.array_equal(a, b), "camera %d: %d pixels differ" % (case, int((a != b).any(-1).sum()))
+        for key in ("primary_rays", "refract_calls", "entered", "exited", "lost"):
+            assert getattr(sa, key) == getattr(sb, key), (case, key)
+    assert with_sky >= 30          # most of these cameras get a plan
+
+
 def test_render_bands_and_stripes_compose(bz, oracle_built):
     """row bands and round-robin stripes reproduce the full frame byte for byte (multi-GPU sharding, one device)"""
     import torch
