@@ -18,7 +18,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_PREPROCESS = 0, -1, -2, -3, -4
 STATUS_NONE, STATUS_INSIDE, STATUS_OUTSIDE = 0, 1, 2
 WHAT_NONE, WHAT_INTERSECT = 3, 4
 NO_PATCH = 0xFFFFFFFF
-MODE_BRUTE, MODE_CULLED, MODE_LANES = 0, 1, 2
+MODE_BRUTE, MODE_CULLED, MODE_LANES, MODE_FAST = 0, 1, 2, 3
 PATCH_WORDS = 64
 
 

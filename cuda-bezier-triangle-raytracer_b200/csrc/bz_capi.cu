@@ -26,6 +26,8 @@ cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job 
 cudaError_t bz_launch_pass(const bz_tables &tables, const bz_job &desc, const float *start, const float *dir, uint32_t *patch, uint64_t count, cudaStream_t stream);
 cudaError_t bz_launch_sky(const bz_job &desc, const uint32_t *d_tiles, uint32_t count, cudaStream_t stream);
 cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta);
+cudaError_t bz_launch_warp_trace_fast(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream);      // csrc/bz_trace.cu built with -DBZ_FAST
+cudaError_t bz_warp_trace_occupancy_fast(int *out_ctas_per_sm, int *out_rays_per_cta);
 cudaError_t bz_launch_emit(const bz_emitter &em, const bz_belts &belts, uint64_t first, uint64_t count, float *start, float *dir, uint32_t *patch,
                            cudaStream_t stream);
 cudaError_t bz_launch_group_by_patch(const uint32_t *patch, uint64_t count, uint32_t patches, uint32_t ways, uint32_t *counts,
@@ -130,6 +132,12 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   *out_lens = nullptr;
   if(h_patches == nullptr && patch_count != 0u) { return bz_fail(BZ_ERR_INVALID, "h_patches is null"); }
   if(patch_count >= (1u << 28)) { return bz_fail(BZ_ERR_INVALID, "too many patches"); }
+  // the follow hop indexes the tables with the neighbour indices (bezierMesh.cpp:213-217): a bad one would be a wild device read
+  for(uint32_t i = 0u; i < patch_count; ++i) {
+    for(int k = 0; k < 3; ++k) {
+      if(h_patches[i].neighbours[k] >= patch_count) { return bz_fail(BZ_ERR_INVALID, "patch " + std::to_string(i) + ": neighbour index out of range"); }
+    }
+  }
   int rc = bz_check_device(device);
   if(rc != BZ_OK) { return rc; }
   BZ_CUDA(cudaSetDevice(device));
@@ -218,7 +226,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
 }
 
 int bz_lens_set_mode(bz_lens *lens, uint32_t mode) {
-  if(lens == nullptr || mode > BZ_MODE_LANES) { return bz_fail(BZ_ERR_INVALID, "bad lens or mode"); }
+  if(lens == nullptr || mode > BZ_MODE_FAST) { return bz_fail(BZ_ERR_INVALID, "bad lens or mode"); }
   lens->mode = mode;
   return BZ_OK;
 }
@@ -291,8 +299,7 @@ static void bz_outline_boxes(const bz_bvh &bvh, std::vector<float> &out) {
 static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<uint32_t> &lens_tiles, std::vector<uint32_t> &sky_tiles) {
   bz_camera const &cam = desc.camera;
   uint32_t const side = desc.tile_side;
-  if(std::getenv("BZ_B200_NO_PLAN") != nullptr) { return false; }                    // tuning runs only
-  if(lens->mode != BZ_MODE_CULLED || lens->outline.empty() || lens->tables.always_count != 0u || side * side > 1024u) { return false; }
+  if((lens->mode != BZ_MODE_CULLED && lens->mode != BZ_MODE_FAST) || lens->outline.empty() || lens->tables.always_count != 0u || side * side > 1024u) { return false; }
   double const m[3][3] = { { cam.right[0], cam.up[0], cam.forward[0] }, { cam.right[1], cam.up[1], cam.forward[1] }, { cam.right[2], cam.up[2], cam.forward[2] } };
   double const det = m[0][0] * (m[1][1] * m[2][2] - m[1][2] * m[2][1]) - m[0][1] * (m[1][0] * m[2][2] - m[1][2] * m[2][0]) + m[0][2] * (m[1][0] * m[2][1] - m[1][1] * m[2][0]);
   double scale = 0.0;
@@ -368,7 +375,7 @@ static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<u
   }
   // the tiles many boxes project onto (silhouette of the body: thick projections, grazing rays, the costliest packets of the
   // frame) are handed out first, so the persistent grid ends on cheap tiles; within a weight the outside-in order stays
-  if(std::getenv("BZ_B200_NO_SORT") == nullptr) {                                     // tuning runs only
+  {
     std::vector<uint32_t> index(lens_tiles.size());
     for(uint32_t i = 0u; i < index.size(); ++i) { index[i] = i; }
     std::stable_sort(index.begin(), index.end(), [&](uint32_t a, uint32_t b) { return weight[a] > weight[b]; });
@@ -405,7 +412,6 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
       // 0.58 -> 0.48 ms with 16 x 16 tiles), so the tiles shrink, down to 8 packets, until there are enough of them
       auto tiles_of = [&](uint32_t s) { return (uint64_t)((desc.camera.width + s - 1u) / s) * ((desc.rows + s - 1u) / s); };
       while(side > 4u && (uint64_t)side * side * spp >= 1024u && tiles_of(side) < 16ull * (uint64_t)lens->sm_count) { side /= 2u; }
-      if(const char *env = std::getenv("BZ_B200_TILE")) { side = (uint32_t)std::max(2, std::atoi(env)); }     // tuning runs only (power of two)
       if((uint64_t)side * side * spp >= (1ull << 31)) { return bz_fail(BZ_ERR_INVALID, "too many samples per pixel"); }
       // divisions by job constants become multiplications (exact while n * d < 2^32: n < tile_rays + 32 for spp,
       // n < spp for strata, n < rows for stripe_rows)
@@ -426,7 +432,7 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
       // the tiles that can meet the lens go to the trace kernel, the others to bz_sky_kernel; the plan of the last frame
       // is kept (same camera, same band: nothing to do)
       auto &plan = lens->plan;
-      bool const same = lens->mode == BZ_MODE_CULLED && plan.valid && std::memcmp(&plan.camera, &desc.camera, sizeof(bz_camera)) == 0 && plan.row0 == desc.row0 && plan.rows == desc.rows
+      bool const same = (lens->mode == BZ_MODE_CULLED || lens->mode == BZ_MODE_FAST) && plan.valid && std::memcmp(&plan.camera, &desc.camera, sizeof(bz_camera)) == 0 && plan.row0 == desc.row0 && plan.rows == desc.rows
                      && plan.stripe_rows == desc.stripe_rows && plan.rank == desc.stripe_rank && plan.ranks == desc.stripe_ranks && plan.side == side;
       if(!same) {
         plan.valid = false;
@@ -465,7 +471,8 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
     if(desc.tile_count >= 0xffffffffull) { return bz_fail(BZ_ERR_INVALID, "job too large"); }
     // persistent grid: every resident CTA slot of the device, or fewer when the job has fewer tiles
     int perSm = 0, raysPerCta = 0;
-    BZ_CUDA(bz_warp_trace_occupancy(&perSm, &raysPerCta));
+    if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_warp_trace_occupancy_fast(&perSm, &raysPerCta)); }
+    else { BZ_CUDA(bz_warp_trace_occupancy(&perSm, &raysPerCta)); }
     grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * (uint64_t)std::max(perSm, 1), desc.tile_count);
   }
   BZ_CUDA(cudaEventRecord(lens->ev_begin, stream));
@@ -474,7 +481,11 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
     bz_tables tables = lens->tables;
     if(lens->mode == BZ_MODE_LANES) { tables.packet_count = 0u; }
     if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, lens->d_tiles + desc.tile_count, sky_count, stream)); ++lens->launches; }
-    if(grid != 0) { BZ_CUDA(bz_launch_warp_trace(job, tables, desc, grid, stream)); ++lens->launches; }
+    if(grid != 0) {
+      if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_warp_trace_fast(job, tables, desc, grid, stream)); }
+      else { BZ_CUDA(bz_launch_warp_trace(job, tables, desc, grid, stream)); }
+      ++lens->launches;
+    }
   }
   BZ_CUDA(cudaEventRecord(lens->ev_end, stream));
   lens->last_stream = stream;
@@ -826,6 +837,7 @@ int bz_illuminate(bz_lens *lens, const bz_emitter *emitter, const bz_target *tar
   uint64_t rays = 0u;
   int rc = bz_check_emitter(emitter, &rays);
   if(rc != BZ_OK) { return rc; }
+  if(rays >= (1ull << 32)) { return bz_fail(BZ_ERR_INVALID, "more than 2^32 - 1 emitter rays in one call (the grouping cursors are 32-bit)"); }
   bz_belts table;
   rc = bz_make_belts(emitter->belts, table);
   if(rc != BZ_OK) { return rc; }

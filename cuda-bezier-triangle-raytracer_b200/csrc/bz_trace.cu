@@ -28,9 +28,21 @@
 // Which of walk / stage A / stage B runs next is decided by queue levels, so the two stages always run on full
 // 32-lane batches except when a pass runs dry.
 // Compiled with -fmad=false (see bz_math.cuh); the box tests use explicit FMAs, they only have to be conservative.
+// The file is compiled twice (Makefile): as the parity build (-fmad=false, IEEE division and square root, bit-exact with
+// the reference) and, with -DBZ_FAST -fmad=true, as the fast build behind BZ_MODE_FAST (csrc/bz_math.cuh says what
+// changes).  Each build lives in its own namespace; the launchers of the fast build carry the suffix _fast.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <math.h>
 #include "bz_device.h"
+#if defined(BZ_FAST)
+#define BZ_NS bz_fast
+#define BZ_SYM(name) name##_fast
+#else
+#define BZ_NS bz_exact
+#define BZ_SYM(name) name
+#endif
+namespace BZ_NS {
 #include "bz_math.cuh"
 
 #ifndef BZ_GROUPS
@@ -95,8 +107,33 @@ __device__ __forceinline__ void bzw_unpack_cull(const float4 *p, bz_cull_rec &c,
   index = __float_as_uint(r3.w);
 }
 
-// control points and dirB: words 0..32 of the stage-B record: (x, y) of the ten control points, their z, dirB
-// (words 33..35 of float4 #8 are the first divider normal)
+// ---- stage B on the packed FP32 pipe (sm_100a FMUL2 / FFMA2: two FP32 operations per issue slot) ----
+// The control points are kept as (x, y) pairs + z, the x and y components of bz_interpolate / bz_normal go through
+// __fmul2_rn / __ffma2_rn, z stays scalar.  Every component sees the same IEEE operations in the same order as in
+// bz_math.cuh, so the results are bit-identical (tests compare with the oracle).  A packed sum a + b is written
+// fma(b, one, a) with `one` = 1.0f read from the job descriptor: exactly a + b, and a form ptxas cannot contract -- it
+// fuses __fadd2_rn(__fmul2_rn(p, q), a) into one FFMA2 (a single rounding) even under -fmad=false.
+__device__ __forceinline__ float2 bzw_mul2(float2 a, float s) { return __fmul2_rn(a, make_float2(s, s)); }
+#if defined(BZ_FAST)
+__device__ __forceinline__ float2 bzw_add2(float2 a, float2 b, float) { return __fadd2_rn(a, b); }      // (ptxas fuses a product feeding it into one FFMA2)
+#else
+__device__ __forceinline__ float2 bzw_add2(float2 a, float2 b, float one) { return __ffma2_rn(b, make_float2(one, one), a); }
+#endif
+
+// K1 and K3 are the same bits in both builds: IEEE operations that never contract (__fmul_rn / __fadd_rn / __fdiv_rn /
+// __fsqrt_rn), three-term sums as a0 + (a1 + a2)
+__device__ __forceinline__ float bzw_dot_rn(const bzv3 &a, const bzv3 &b) { return __fadd_rn(__fmul_rn(a.x, b.x), __fadd_rn(__fmul_rn(a.y, b.y), __fmul_rn(a.z, b.z))); }
+__device__ __forceinline__ bzv3 bzw_normalized_rn(const bzv3 &v) {
+  const float z = bzw_dot_rn(v, v);
+  if(z > 0.0f) {
+    const float n = __fsqrt_rn(z);
+    return bz_v(__fdiv_rn(v.x, n), __fdiv_rn(v.y, n), __fdiv_rn(v.z, n));
+  }
+  return v;
+}
+
+#if defined(BZ_FAST)
+// control points and dirB: words 0..32 of the stage-B record ((x, y) of the ten control points, their z, dirB)
 __device__ __forceinline__ void bzw_load_newton_root(const float4 *p, bz_newton_rec &t) {
   float w[36];
 #pragma unroll
@@ -108,23 +145,13 @@ __device__ __forceinline__ void bzw_load_newton_root(const float4 *p, bz_newton_
   for(int i = 0; i < 10; ++i) { t.cp[i] = bz_v(w[2 * i], w[2 * i + 1], w[20 + i]); }
   t.dir_b = bz_v(w[30], w[31], w[32]);
 }
-
-#ifndef BZ_SCALAR_STAGE_B
-// ---- stage B on the packed FP32 pipe (sm_100a FMUL2 / FFMA2: two FP32 operations per issue slot) ----
-// The control points are kept as (x, y) pairs + z, the x and y components of bz_interpolate / bz_normal go through
-// __fmul2_rn / __ffma2_rn, z stays scalar.  Every component sees the same IEEE operations in the same order as in
-// bz_math.cuh, so the results are bit-identical (tests compare with the oracle).  A packed sum a + b is written
-// fma(b, one, a) with `one` = 1.0f read from the job descriptor: exactly a + b, and a form ptxas cannot contract -- it
-// fuses __fadd2_rn(__fmul2_rn(p, q), a) into one FFMA2 (a single rounding) even under -fmad=false.
+#else
 struct bzw_newton2 {
   float2 xy[10];
   float  z[10];
   bzv3   dir_b;
   float  one;
 };
-
-__device__ __forceinline__ float2 bzw_mul2(float2 a, float s) { return __fmul2_rn(a, make_float2(s, s)); }
-__device__ __forceinline__ float2 bzw_add2(float2 a, float2 b, float one) { return __ffma2_rn(b, make_float2(one, one), a); }
 
 __device__ __forceinline__ void bzw_load_newton2(const float4 *p, float one, bzw_newton2 &t) {
   float w[36];
@@ -210,43 +237,39 @@ __device__ __forceinline__ void bzw_load_newton_side(const float4 *p, bz_newton_
 // IEEE division the per-ray code would do).
 __device__ __forceinline__ void bzw_primary_ray(const bz_camera &cam, float two_over_w, float two_over_h, uint32_t px, uint32_t py, uint32_t sx, uint32_t sy,
                                                 bzv3 &start, bzv3 &dir) {
-  float strata = (float)cam.strata;
-  float fu = (float)px + ((float)sx + 0.5f) / strata;
-  float fv = (float)py + ((float)sy + 0.5f) / strata;
-  float a = (fu * two_over_w - 1.0f) * cam.half_w;
-  float b = (1.0f - fv * two_over_h) * cam.half_h;
-  bzv3 offset = bz_v(cam.right[0] * a + cam.up[0] * b, cam.right[1] * a + cam.up[1] * b, cam.right[2] * a + cam.up[2] * b);
+  const float strata = (float)cam.strata;
+  const float fu = __fadd_rn((float)px, __fdiv_rn(__fadd_rn((float)sx, 0.5f), strata));
+  const float fv = __fadd_rn((float)py, __fdiv_rn(__fadd_rn((float)sy, 0.5f), strata));
+  const float a = __fmul_rn(__fadd_rn(__fmul_rn(fu, two_over_w), -1.0f), cam.half_w);
+  const float b = __fmul_rn(__fadd_rn(1.0f, -__fmul_rn(fv, two_over_h)), cam.half_h);
+  const bzv3 offset = bz_v(__fadd_rn(__fmul_rn(cam.right[0], a), __fmul_rn(cam.up[0], b)), __fadd_rn(__fmul_rn(cam.right[1], a), __fmul_rn(cam.up[1], b)),
+                           __fadd_rn(__fmul_rn(cam.right[2], a), __fmul_rn(cam.up[2], b)));
   bzv3 raw;
   if(cam.ortho != 0u) {
-    start = bz_v(cam.eye[0] + offset.x, cam.eye[1] + offset.y, cam.eye[2] + offset.z);
+    start = bz_v(__fadd_rn(cam.eye[0], offset.x), __fadd_rn(cam.eye[1], offset.y), __fadd_rn(cam.eye[2], offset.z));
     raw = bz_v(cam.forward[0], cam.forward[1], cam.forward[2]);
   }
   else {
     start = bz_v(cam.eye[0], cam.eye[1], cam.eye[2]);
-    raw = bz_v(cam.forward[0] + offset.x, cam.forward[1] + offset.y, cam.forward[2] + offset.z);
+    raw = bz_v(__fadd_rn(cam.forward[0], offset.x), __fadd_rn(cam.forward[1], offset.y), __fadd_rn(cam.forward[2], offset.z));
   }
-  dir = bz_normalized(raw);    // Ray::Ray, 3dGeomUtil.h:176-178
+  dir = bzw_normalized_rn(raw);    // Ray::Ray, 3dGeomUtil.h:176-178
 }
 
 // K3: checker on the background plane, Plane::intersect semantics (3dGeomUtil.h:279-296).
 __device__ __forceinline__ uint32_t bzw_shade_background(const bz_scene &sc, const bzv3 &start, const bzv3 &dir) {
-  bzv3 n = bz_v(sc.bg_plane[0], sc.bg_plane[1], sc.bg_plane[2]);
-  float cosine = bz_dot(dir, n);
+  const bzv3 n = bz_v(sc.bg_plane[0], sc.bg_plane[1], sc.bg_plane[2]);
+  const float cosine = bzw_dot_rn(dir, n);
   if(!(fabsf(cosine) >= BZ_PLANE_EPSILON)) { return sc.value_lost; }
-  float distance = (sc.bg_plane[3] - bz_dot(n, start)) / cosine;
+  const float distance = __fdiv_rn(__fadd_rn(sc.bg_plane[3], -bzw_dot_rn(n, start)), cosine);
   if(!(distance > 0.0f)) { return sc.value_lost; }
-  bzv3 p = bz_v(start.x + distance * dir.x, start.y + distance * dir.y, start.z + distance * dir.z);
-  float ca = floorf(bz_dot(p, bz_v(sc.bg_axis_a[0], sc.bg_axis_a[1], sc.bg_axis_a[2])) / sc.cell);
-  float cb = floorf(bz_dot(p, bz_v(sc.bg_axis_b[0], sc.bg_axis_b[1], sc.bg_axis_b[2])) / sc.cell);
-#ifdef BZ_CHECKER_FMOD
-  float pa = fabsf(fmodf(ca, 2.0f));
-  float pb = fabsf(fmodf(cb, 2.0f));
-#else
+  const bzv3 p = bz_v(__fadd_rn(start.x, __fmul_rn(distance, dir.x)), __fadd_rn(start.y, __fmul_rn(distance, dir.y)), __fadd_rn(start.z, __fmul_rn(distance, dir.z)));
+  const float ca = floorf(__fdiv_rn(bzw_dot_rn(p, bz_v(sc.bg_axis_a[0], sc.bg_axis_a[1], sc.bg_axis_a[2])), sc.cell));
+  const float cb = floorf(__fdiv_rn(bzw_dot_rn(p, bz_v(sc.bg_axis_b[0], sc.bg_axis_b[1], sc.bg_axis_b[2])), sc.cell));
   // |fmodf(c, 2)| for an integral-valued c, computed exactly without the library routine: c/2, floor, the doubling and
   // the difference are all exact in FP32 (and an infinite or NaN c gives NaN either way)
-  float pa = fabsf(ca - 2.0f * floorf(ca * 0.5f));
-  float pb = fabsf(cb - 2.0f * floorf(cb * 0.5f));
-#endif
+  const float pa = fabsf(__fadd_rn(ca, -__fmul_rn(2.0f, floorf(__fmul_rn(ca, 0.5f)))));
+  const float pb = fabsf(__fadd_rn(cb, -__fmul_rn(2.0f, floorf(__fmul_rn(cb, 0.5f)))));
   return (pa != pb) ? sc.value_bright : sc.value_dark;
 }
 
@@ -254,18 +277,18 @@ __device__ __forceinline__ uint32_t bzw_shade_background(const bz_scene &sc, con
 // or BZ_LAND_MISSED.  Plane::intersect semantics (3dGeomUtil.h:279-296).
 __device__ __forceinline__ uint32_t bzw_land_on_target(const bz_job &J, const bzv3 &start, const bzv3 &dir) {
   const bzv3 n = bz_v(J.target_plane[0], J.target_plane[1], J.target_plane[2]);
-  const float cosine = bz_dot(dir, n);
+  const float cosine = bzw_dot_rn(dir, n);
   if(!(fabsf(cosine) >= BZ_PLANE_EPSILON)) { return BZ_LAND_MISSED; }
-  const float distance = (J.target_plane[3] - bz_dot(n, start)) / cosine;
+  const float distance = __fdiv_rn(__fadd_rn(J.target_plane[3], -bzw_dot_rn(n, start)), cosine);
   if(!(distance > 0.0f)) { return BZ_LAND_MISSED; }
-  const bzv3 rel = bz_v(start.x + distance * dir.x - J.target.origin[0], start.y + distance * dir.y - J.target.origin[1],
-                        start.z + distance * dir.z - J.target.origin[2]);
+  const bzv3 rel = bz_v(__fadd_rn(__fadd_rn(start.x, __fmul_rn(distance, dir.x)), -J.target.origin[0]), __fadd_rn(__fadd_rn(start.y, __fmul_rn(distance, dir.y)), -J.target.origin[1]),
+                        __fadd_rn(__fadd_rn(start.z, __fmul_rn(distance, dir.z)), -J.target.origin[2]));
   const bzv3 eu = bz_v(J.target.edge_u[0], J.target.edge_u[1], J.target.edge_u[2]);
   const bzv3 ev = bz_v(J.target.edge_v[0], J.target.edge_v[1], J.target.edge_v[2]);
-  const float su = bz_dot(rel, eu) / bz_dot(eu, eu), sv = bz_dot(rel, ev) / bz_dot(ev, ev);
+  const float su = __fdiv_rn(bzw_dot_rn(rel, eu), bzw_dot_rn(eu, eu)), sv = __fdiv_rn(bzw_dot_rn(rel, ev), bzw_dot_rn(ev, ev));
   if(!(su >= 0.0f && su < 1.0f && sv >= 0.0f && sv < 1.0f)) { return BZ_LAND_MISSED; }
-  const uint32_t bu = min((uint32_t)(su * (float)J.target.bins_u), J.target.bins_u - 1u);
-  const uint32_t bv = min((uint32_t)(sv * (float)J.target.bins_v), J.target.bins_v - 1u);
+  const uint32_t bu = min((uint32_t)__fmul_rn(su, (float)J.target.bins_u), J.target.bins_u - 1u);
+  const uint32_t bv = min((uint32_t)__fmul_rn(sv, (float)J.target.bins_v), J.target.bins_v - 1u);
   return bv * J.target.bins_u + bu;
 }
 
@@ -504,7 +527,7 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             uint32_t sp = 1u, found = (direct_n + 6u) / 7u;
             packet_done = (found <= BZ_CAND_CAP / 2u);
             if(packet_done) {
-              if(lane < found) { P.cand[lane] = ((direct_first + 7u * lane) << 3) | min(7u, direct_n - 7u * lane); }
+              for(uint32_t e = lane; e < found; e += 32u) { P.cand[e] = ((direct_first + 7u * e) << 3) | min(7u, direct_n - 7u * e); }
               if(lane == 0u) { P.stack[0] = 0u; }
               __syncwarp();
             }
@@ -578,6 +601,9 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
             }
             room -= 32u;
           }
+          // a burst of the hierarchy walk pushes up to 32 * BZ_LEAF_PUSH * BZ_WALK_BURST pairs before it looks at the level
+          // again: the direct records above may have used that room up
+          if(room < 32u * BZ_LEAF_PUSH * BZ_WALK_BURST) { paused = true; }
           // the hierarchy: BZ_WALK_BURST steps per lane between two looks at the queue level
           uint32_t steps = 0u;
           while(!paused) {
@@ -647,12 +673,16 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           const float2 nx = make_float2(r0.x, r0.y), ny = make_float2(r0.z, r0.w), nz = make_float2(r1.x, r1.y), kk = make_float2(r1.z, r1.w);
           const float2 cosine = bzw_add2(bzw_mul2(nx, d.x), bzw_add2(bzw_mul2(ny, d.y), bzw_mul2(nz, d.z), one), one);         // bz_dot(d, n)
           const float2 along = bzw_add2(bzw_mul2(nx, s.x), bzw_add2(bzw_mul2(ny, s.y), bzw_mul2(nz, s.z), one), one);          // bz_dot(n, s)
+#if defined(BZ_FAST)
+          const float2 above = __fadd2_rn(kk, make_float2(-along.x, -along.y));
+#else
           const float2 above = __ffma2_rn(along, make_float2(-one, -one), kk);                                                  // k - bz_dot(n, s)
+#endif
           bool pass_a = live && fabsf(cosine.x) >= BZ_PLANE_EPSILON;
           bool pass_b = live && left >= 2u && fabsf(cosine.y) >= BZ_PLANE_EPSILON;
           float2 distance = make_float2(0.0f, 0.0f);
-          if(pass_a) { distance.x = above.x / cosine.x; }
-          if(pass_b) { distance.y = above.y / cosine.y; }
+          if(pass_a) { distance.x = BZ_DIV(above.x, cosine.x); }
+          if(pass_b) { distance.y = BZ_DIV(above.y, cosine.y); }
           pass_a = pass_a && distance.x > 0.0f && fabsf(distance.x) > -r3.z && fabsf(distance.x) > r5.z;     // hIn (word 7), hOut (word 11)
           pass_b = pass_b && distance.y > 0.0f && fabsf(distance.y) > -r3.w && fabsf(distance.y) > r5.w;
           if(__ballot_sync(0xffffffffu, pass_a || pass_b) != 0u) {
@@ -742,13 +772,13 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
           float cosine, distance;
           if(bz_stage_a(c, s, d, first_level, cosine, distance)) {
             bz_newton_rec t;
-#ifndef BZ_SCALAR_STAGE_B
+#if defined(BZ_FAST)
+            bzw_load_newton_root(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
+            if(bz_stage_b_root(c, t, s, d, cosine, distance, hit)) {
+#else
             bzw_newton2 t2;
             bzw_load_newton2(T.newton + (size_t)patch * BZ_NEWTON_F4, J.one, t2);
             if(bz_stage_b_root(c, t2, s, d, cosine, distance, hit)) {
-#else
-            bzw_load_newton_root(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
-            if(bz_stage_b_root(c, t, s, d, cosine, distance, hit)) {
 #endif
               bzw_load_newton_side(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
               bz_stage_b_side(t, d, hit);
@@ -898,6 +928,9 @@ __global__ void __launch_bounds__(32 * BZ_WARPS, BZ_MIN_CTAS) bz_warp_trace_kern
   if(J.stats != nullptr && lane < BZ_NSTAT && P.count[lane] != 0ull) { atomicAdd(J.stats + lane, P.count[lane]); }
 }
 
+}  // namespace BZ_NS
+using namespace BZ_NS;
+
 static size_t bzw_shared_bytes() { return sizeof(bz_warp_pool) * BZ_WARPS; }
 
 static cudaError_t bzw_configure() {
@@ -915,7 +948,7 @@ static cudaError_t bzw_configure() {
   return e;
 }
 
-cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream) {
+cudaError_t BZ_SYM(bz_launch_warp_trace)(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream) {
   cudaError_t e = bzw_configure();
   if(e != cudaSuccess) { return e; }
   if(job == BZ_JOB_RENDER) { bz_warp_trace_kernel<BZ_JOB_RENDER><<<grid, 32 * BZ_WARPS, bzw_shared_bytes(), stream>>>(tables, desc); }
@@ -926,13 +959,14 @@ cudaError_t bz_launch_warp_trace(int job, const bz_tables &tables, const bz_job 
 }
 
 // resident CTAs per SM of the render instantiation (the persistent grid is sized from it)
-cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta) {
+cudaError_t BZ_SYM(bz_warp_trace_occupancy)(int *out_ctas_per_sm, int *out_rays_per_cta) {
   *out_rays_per_cta = BZ_WARPS * BZ_SLOTS;
   cudaError_t e = bzw_configure();
   if(e != cudaSuccess) { return e; }
   return cudaOccupancyMaxActiveBlocksPerMultiprocessor(out_ctas_per_sm, bz_warp_trace_kernel<BZ_JOB_RENDER>, 32 * BZ_WARPS, bzw_shared_bytes());
 }
 
+#if !defined(BZ_FAST)      // the kernels below do none of stage A / B: one copy, in the parity build
 // ---- sky tiles: the tiles of a RENDER job none of whose rays can meet the lens (csrc/bz_capi.cu: bz_plan_tiles) ----
 // Every refract() of such a ray is cNone (one call each, as in the bounce loop), so the pixel is the sum of the background
 // values of its samples: one CTA per tile, one thread per pixel, a plain store into the accumulator (no other kernel
@@ -1018,3 +1052,4 @@ cudaError_t bz_launch_pass(const bz_tables &tables, const bz_job &desc, const fl
   bz_pass_kernel<<<(unsigned)((count + 255u) / 256u), 256, 0, stream>>>(tables, desc, start, dir, patch, count);
   return cudaGetLastError();
 }
+#endif

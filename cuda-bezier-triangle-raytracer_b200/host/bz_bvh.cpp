@@ -48,7 +48,7 @@ struct Binary {
 };
 
 constexpr int cBins = 16;
-uint32_t cLeafMax = BZ_BVH_LEAF_MAX;   // <= 7 (3 bits in the leaf code)
+constexpr uint32_t cLeafMax = BZ_BVH_LEAF_MAX;   // <= 7 (3 bits in the leaf code)
 constexpr double cKappaLimit = 16.0;
 constexpr double cKappaWideLimit = 65536.0;
 constexpr double cSlackUnit = 1.9073486328125e-06;     // 2^-19; the kernel's per-ray slack is cKappaLimit * cSlackUnit * (|s|_1 + 2 extent)
@@ -149,7 +149,6 @@ void bz_build_bvh(const bz_patch *patches, uint32_t count, bz_bvh &out) {
   out.origin_limit = 0.0f;
   out.packet_nodes.clear();
   out.packet_depth = 0u;
-  if(const char *env = std::getenv("BZ_B200_LEAF")) { cLeafMax = std::min(2, std::max(1, std::atoi(env))); }     // tuning runs only
   Builder b;
   std::vector<uint32_t> prims;     // primitive -> patch
   std::vector<double> kappas(count, std::numeric_limits<double>::infinity());

@@ -110,6 +110,9 @@ typedef struct bz_bezier bz_bezier;   /* host object: BezierMesh, reference/bezi
 #define BZ_MODE_BRUTE   0u   /* every ray tests every patch, reference loop order (bezierMesh.cpp:211) */
 #define BZ_MODE_CULLED  1u   /* exact candidate-set-preserving cull (warp-cooperative packet walk, per-lane walk for incoherent packets), then the same stage A/B */
 #define BZ_MODE_LANES   2u   /* as BZ_MODE_CULLED with the packet walk switched off: every ray walks the hierarchy on its own lane (test / comparison arm) */
+#define BZ_MODE_FAST    3u   /* BZ_MODE_CULLED's kernel built with FMA contraction, MUFU reciprocal / reciprocal square root and FP32 cos2: NOT bit-exact;
+                                held to north_star's tolerance instead (status exact, patch index exact away from patch edges, points and directions
+                                within 1e-5 relative, >= 90 % of the pixels identical).  Ray generation and shading are the same bits in every mode. */
 
 const char *bz_last_error(void);
 int  bz_device_count(int *out_count);
