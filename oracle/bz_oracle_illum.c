@@ -1,7 +1,11 @@
 /* TEST INFRASTRUCTURE ONLY -- CPU restatement of the illumination mode's two non-tracing stages, used as the checker of
- * bz_emit_rays / bz_trace_to_target (include/bz_capi.h).  Parity unpinned by the reference: the reference has the emitter
- * sampler only (no target, no tests of it), and its random stream (std::ranlux24_base) is replaced by the counter-based
- * generator the C ABI defines, so this file restates
+ * bz_emit_rays / bz_trace_to_target (include/bz_capi.h).
+ * Pinned to the reference for the sampler: oracle/_ref holds the real UniformHemisphere (reference/hostUtil.cpp compiled from
+ * /root/reference); tests/test_illumination.py feeds its getRandom() the draws of the generator below and compares belt
+ * table, patch index and direction with this file bit for bit (golden copy: tests/golden/golden_hemisphere.npz).  The
+ * reference's random stream (std::ranlux24_base) is replaced by the counter-based generator the C ABI defines -- both turn a
+ * 24-bit draw o into o * 2^-24 -- and the reference has no target rectangle (README.md:161-194 was never written): the
+ * landing stage is this repository's definition, unpinned.  This file restates
  *   UniformHemisphere::UniformHemisphere   reference/hostUtil.cpp:3-14
  *   UniformHemisphere::getRandom           reference/hostUtil.cpp:16-29   (acos / sin / cos in double, as ::acos(float) resolves)
  *   Plane::intersect                       reference/3dGeomUtil.h:279-296 (for the landing point on the target)

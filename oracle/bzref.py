@@ -102,6 +102,8 @@ def load(as_written=False):
         "bzref_generate_rays": (None, [C.POINTER(Camera), u32, u32, fp, fp]),
         "bzref_render": (u64, [vp, C.POINTER(Camera), C.POINTER(Scene), u32, u32, u32, C.POINTER(C.c_uint8),
                                C.POINTER(Stats), C.c_int]),
+        "bzref_hemisphere": (u32, [u32, fp, up]),
+        "bzref_hemisphere_random": (u64, [u32, up, up, u64, fp, up]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -316,3 +318,35 @@ def make_scene(bg_x=12.0, cell=1.0, dark=25, bright=230, lost=0, max_crossings=2
     sc.cell = cell
     sc.value_dark, sc.value_bright, sc.value_lost, sc.max_crossings = dark, bright, lost, max_crossings
     return sc
+
+
+def hemisphere(belts):
+    """belt table of the REAL UniformHemisphere constructor (reference/hostUtil.cpp:3-14) -> (patch count, width[belts], first[belts])"""
+    width, first = np.zeros(belts, np.float32), np.zeros(belts, np.uint32)
+    count = load().bzref_hemisphere(belts, _fp(width), _up(first))
+    return int(count), width, first
+
+
+def hemisphere_random(belts, draw1, draw2):
+    """the REAL UniformHemisphere::getRandom (reference/hostUtil.cpp:16-29) with its engine set so that the two draws of call i
+    are the 24-bit integers draw1[i], draw2[i] (u = draw * 2^-24) -> (direction[n,3], patch[n])"""
+    d1, d2 = np.ascontiguousarray(draw1, np.uint32), np.ascontiguousarray(draw2, np.uint32)
+    assert d1.shape == d2.shape and d1.ndim == 1 and int(max(d1.max(initial=0), d2.max(initial=0))) < (1 << 24)
+    direction, patch = np.zeros((d1.size, 3), np.float32), np.zeros(d1.size, np.uint32)
+    wrong = load().bzref_hemisphere_random(belts, _up(d1), _up(d2), d1.size, _fp(direction), _up(patch))
+    assert wrong == 0, "the reference engine did not deliver the chosen draws on %d calls" % wrong
+    return direction, patch
+
+
+def abi_draws(seed, first, count):
+    """the C ABI's counter-based generator (include/bz_capi.h, bz_emitter): 24-bit draws (draw1, draw2) of rays [first, first + count)"""
+    ray = np.arange(first, first + count, dtype=np.uint64)
+    out = []
+    with np.errstate(over="ignore"):
+        for draw in (0, 1):
+            z = np.uint64(seed) + (np.uint64(2) * ray + np.uint64(draw + 1)) * np.uint64(0x9E3779B97F4A7C15)
+            z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            z = z ^ (z >> np.uint64(31))
+            out.append((z >> np.uint64(40)).astype(np.uint32))
+    return out[0], out[1]

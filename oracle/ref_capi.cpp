@@ -8,7 +8,7 @@
 //
 // Everything that is arithmetic on the hot path is done by the reference's own code:
 // Mesh::standardizeVertices/standardizeNormals, BezierMesh::BezierMesh, BezierTriangle::intersect,
-// BezierMesh::intersect, BezierLens::refract.  What this file adds is
+// BezierMesh::intersect, BezierLens::refract, UniformHemisphere (belt table and getRandom).  What this file adds is
 //   * table dumping (private BezierTriangle fields -> bz_patch),
 //   * bzref_intersect_batch: BezierMesh::intersect does not report WHICH patch was hit
 //     (bezierMesh.cpp:206-227 returns no index), so the 20-line loop is repeated here around the
@@ -39,11 +39,13 @@
 #include <functional>
 #include <unordered_map>
 #include <unordered_set>
+#include <random>
 #include "stl_reader.h"
 
 // Expose BezierTriangle's private fields to the table dump below (layout is unaffected).
 #define private public
 #include "bezierLens.h"
+#include "hostUtil.h"
 #undef private
 
 #include "bz_capi.h"
@@ -429,6 +431,42 @@ uint64_t bzref_render(void *aLens, bz_camera const *aCamera, bz_scene const *aSc
     aStats->lost += counters.mLost.load();
   }
   return counters.mPrimary.load();
+}
+
+// ---- UniformHemisphere, reference/hostUtil.h:8-24, hostUtil.cpp:3-29 (illumination mode) ----
+
+// belt table of the REAL constructor: (patch width, patches before the belt) per belt -> patch count
+uint32_t bzref_hemisphere(uint32_t aBelts, float *aWidth, uint32_t *aFirst) {
+  UniformHemisphere hemisphere(aBelts);
+  for(uint32_t i = 0u; i < aBelts; ++i) {
+    if(aWidth != nullptr) { aWidth[i] = hemisphere.mBelts[i].first; }
+    if(aFirst != nullptr) { aFirst[i] = hemisphere.mBelts[i].second; }
+  }
+  return hemisphere.getPatchCount();
+}
+
+// The REAL getRandom() fed with chosen draws.  std::ranlux24_base is subtract_with_carry_engine<uint_fast32_t, 24, 10, 24>: with
+// index 0 and no carry its next two outputs are x[14] - x[0] and x[15] - x[1], and std::uniform_real_distribution<float>
+// turns a 24-bit output o into o * 2^-24 * (b - a) + a (one draw, generate_canonical<float, 24>).  The engine state is set
+// through its public stream extractor (24 words, carry, index), so the two draws of a call are aDraw1[i], aDraw2[i] (< 2^24):
+// u1 = aDraw1 * 2^-24 for the incidence, u2 = aDraw2 * 2^-24 for the turn -- the map the C ABI defines for its own generator.
+// -> 0, or the number of calls whose engine did not deliver the chosen draws (self-check)
+uint64_t bzref_hemisphere_random(uint32_t aBelts, uint32_t const *aDraw1, uint32_t const *aDraw2, uint64_t aCount, float *aDirection, uint32_t *aPatch) {
+  UniformHemisphere hemisphere(aBelts);
+  uint64_t wrong = 0u;
+  for(uint64_t i = 0u; i < aCount; ++i) {
+    std::ostringstream text;
+    for(int word = 0; word < 24; ++word) { text << (word == 14 ? aDraw1[i] : (word == 15 ? aDraw2[i] : 0u)) << ' '; }
+    text << "0 0";
+    std::istringstream state(text.str());
+    state >> hemisphere.mRandomGenerator;
+    std::ranlux24_base probe = hemisphere.mRandomGenerator;
+    if(probe() != aDraw1[i] || probe() != aDraw2[i]) { ++wrong; }
+    auto [direction, index] = hemisphere.getRandom();
+    aDirection[i * 3u] = direction(0); aDirection[i * 3u + 1u] = direction(1); aDirection[i * 3u + 2u] = direction(2);
+    aPatch[i] = index;
+  }
+  return wrong;
 }
 
 }

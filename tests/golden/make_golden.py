@@ -3,7 +3,7 @@
     make -C oracle && python tests/golden/make_golden.py
 The vectors pin (a) the bz_patch tables of BezierMesh(Mesh), (b) BezierMesh::intersect and (c) two successive
 BezierLens::refract crossings on seeded rays, so that the plain-C oracle, the host preprocessing and the CUDA path can
-be checked on machines without the reference (the GPU box)."""
+be checked on machines without the reference (the GPU box); golden_hemisphere.npz pins (d) UniformHemisphere."""
 import os
 import sys
 
@@ -40,5 +40,21 @@ def main():
               os.path.getsize(out), "bytes")
 
 
+def hemisphere():
+    """UniformHemisphere (reference/hostUtil.cpp:3-29): belt tables and getRandom() on the draws of the C ABI's generator"""
+    seed, rays = 424242, 2048
+    out = {"seed": np.uint64(seed), "rays": np.uint32(rays)}
+    draw1, draw2 = bzref.abi_draws(seed, 0, rays)
+    for belts in (1, 2, 7, 16, 64, 128):
+        count, width, first = bzref.hemisphere(belts)
+        direction, patch = bzref.hemisphere_random(belts, draw1, draw2)
+        out.update({"count_%d" % belts: np.uint32(count), "width_%d" % belts: width, "first_%d" % belts: first,
+                    "direction_%d" % belts: direction, "patch_%d" % belts: patch})
+    path = os.path.join(HERE, "golden_hemisphere.npz")
+    np.savez_compressed(path, **out)
+    print("hemisphere", os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
+    hemisphere()
     main()
