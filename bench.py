@@ -37,6 +37,7 @@ def parse_args():
     p.add_argument("--workload", default=None)
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="target wall time of one CPU-baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--pipeline", default="auto", choices=["auto", "persistent", "wavefront"], help="how the lens tiles are traced (bz_lens_set_pipeline)")
     p.add_argument("--mode", default="exact", choices=["exact", "fast"],
                    help="exact: the parity build (-fmad=false, bit-exact with the reference); fast: BZ_MODE_FAST (FMA, MUFU reciprocals; north_star's tolerance)")
     return p.parse_args()
@@ -189,6 +190,7 @@ def main_ours(args, name):
     lens = bz.BezierLens(spec["ri"], bezier, device=local)
     if args.mode == "fast":
         lens.set_mode(bz.MODE_FAST)
+    lens.set_pipeline({"auto": bz.PIPELINE_AUTO, "persistent": bz.PIPELINE_PERSISTENT, "wavefront": bz.PIPELINE_WAVEFRONT}[args.pipeline])
     setup_s = time.perf_counter() - t_setup
     cam, scene = bz.make_camera(spec["width"], spec["height"], **cam_kw), bz.make_scene(**scene_kw)
     width, height, spp = spec["width"], spec["height"], spec["strata"] ** 2
@@ -316,7 +318,7 @@ def main_ours(args, name):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": name, "patches": lens.patch_count, "image": "%dx%d" % (width, height), "spp": spp, "primary_rays_per_step": frame_rays,
                        "refractive_index": spec["ri"], "max_crossings": spec["max_crossings"], "parallelism": "row stripes of %d x %d ranks" % (stripe, world),
-                       "l2": "flushed between steps (256 MiB fill)", "mode": "culled (exact candidate-set-preserving BVH)" + (", BZ_MODE_FAST arithmetic" if args.mode == "fast" else ""), "fmad": args.mode == "fast",
+                       "l2": "flushed between steps (256 MiB fill)", "mode": "culled (exact candidate-set-preserving BVH)" + (", BZ_MODE_FAST arithmetic" if args.mode == "fast" else ""), "fmad": args.mode == "fast", "pipeline": args.pipeline,
                        "setup_s": setup_s},
             "e2e": {"value": frame_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(bz.load().bz_sizeof_camera() + bz.load().bz_sizeof_scene()),
                     "d2h_bytes_per_step": width * height * 4, "ms_per_step": e2e_s * 1e3,

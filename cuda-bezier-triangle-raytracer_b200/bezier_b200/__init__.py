@@ -19,6 +19,8 @@ STATUS_NONE, STATUS_INSIDE, STATUS_OUTSIDE = 0, 1, 2
 WHAT_NONE, WHAT_INTERSECT = 3, 4
 NO_PATCH = 0xFFFFFFFF
 MODE_BRUTE, MODE_CULLED, MODE_LANES, MODE_FAST = 0, 1, 2, 3
+PIPELINE_AUTO, PIPELINE_PERSISTENT, PIPELINE_WAVEFRONT = 0, 1, 2
+ERR_OVERFLOW = -5
 PATCH_WORDS = 64
 
 
@@ -128,6 +130,8 @@ SIGNATURES = {
     "bz_lens_destroy": (_int, [_vp]),
     "bz_lens_set_mode": (_int, [_vp, _u32]),
     "bz_lens_patch_count": (_int, [_vp, C.POINTER(_u32)]),
+    "bz_lens_set_pipeline": (_int, [_vp, _u32]),
+    "bz_lens_check": (_int, [_vp]),
     "bz_lens_info": (_int, [_vp, C.POINTER(_u32 * 4)]),
     "bz_refract_batch": (_int, [_vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
     "bz_refract_batch_host": (_int, [_vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
@@ -418,6 +422,15 @@ class BezierLens:
     def set_mode(self, mode):
         _check(self.lib.bz_lens_set_mode(self.h, mode))
         return self
+
+    def set_pipeline(self, pipeline):
+        """PIPELINE_AUTO / PIPELINE_PERSISTENT / PIPELINE_WAVEFRONT for the render calls (same bits either way)"""
+        _check(self.lib.bz_lens_set_pipeline(self.h, pipeline))
+        return self
+
+    def check(self):
+        """synchronise and raise if a device-side work list overflowed since the last check"""
+        _check(self.lib.bz_lens_check(self.h))
 
     def info(self):
         out = (_u32 * 4)()

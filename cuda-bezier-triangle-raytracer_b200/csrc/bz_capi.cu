@@ -28,6 +28,8 @@ cudaError_t bz_launch_sky(const bz_job &desc, const uint32_t *d_tiles, uint32_t 
 cudaError_t bz_warp_trace_occupancy(int *out_ctas_per_sm, int *out_rays_per_cta);
 cudaError_t bz_launch_warp_trace_fast(int job, const bz_tables &tables, const bz_job &desc, int grid, cudaStream_t stream);      // csrc/bz_trace.cu built with -DBZ_FAST
 cudaError_t bz_warp_trace_occupancy_fast(int *out_ctas_per_sm, int *out_rays_per_cta);
+cudaError_t bz_launch_wave_pass(const bz_tables &tables, const bz_job &desc, const bz_wave &wave, int sm_count, cudaStream_t stream);           // csrc/bz_wave.cu
+cudaError_t bz_launch_wave_pass_fast(const bz_tables &tables, const bz_job &desc, const bz_wave &wave, int sm_count, cudaStream_t stream);
 cudaError_t bz_launch_emit(const bz_emitter &em, const bz_belts &belts, uint64_t first, uint64_t count, float *start, float *dir, uint32_t *patch,
                            cudaStream_t stream);
 cudaError_t bz_launch_group_by_patch(const uint32_t *patch, uint64_t count, uint32_t patches, uint32_t ways, uint32_t *counts,
@@ -74,6 +76,11 @@ struct bz_lens {
   cudaEvent_t ev_plan;                // the upload of d_tiles (a call on another stream waits for it)
   cudaStream_t plan_stream;
   uint32_t   launches;                // kernels of the most recent call
+  // RENDER, wavefront pipeline (csrc/bz_wave.cu): ray slots and candidate list of one chunk of tiles
+  uint32_t   pipeline;                // BZ_PIPELINE_*
+  bz_wave    wave;
+  void      *d_wave;                  // one allocation behind the pointers of `wave`
+  size_t     wave_bytes;
 };
 
 static void bz_outline_boxes(const bz_bvh &bvh, std::vector<float> &out);
@@ -111,7 +118,7 @@ int bz_lens_destroy(bz_lens *lens) {
   if(lens == nullptr) { return BZ_OK; }
   cudaSetDevice(lens->device);
   cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_pairs); cudaFree(lens->d_nodes); cudaFree(lens->d_packet);
-  cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch); cudaFree(lens->d_illum); cudaFree(lens->d_tiles);
+  cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch); cudaFree(lens->d_illum); cudaFree(lens->d_tiles); cudaFree(lens->d_wave);
   if(lens->ev_begin) { cudaEventDestroy(lens->ev_begin); }
   if(lens->ev_plan) { cudaEventDestroy(lens->ev_plan); }
   if(lens->ev_end) { cudaEventDestroy(lens->ev_end); }
@@ -228,6 +235,26 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
 int bz_lens_set_mode(bz_lens *lens, uint32_t mode) {
   if(lens == nullptr || mode > BZ_MODE_FAST) { return bz_fail(BZ_ERR_INVALID, "bad lens or mode"); }
   lens->mode = mode;
+  return BZ_OK;
+}
+
+int bz_lens_set_pipeline(bz_lens *lens, uint32_t pipeline) {
+  if(lens == nullptr || pipeline > BZ_PIPELINE_WAVEFRONT) { return bz_fail(BZ_ERR_INVALID, "bad lens or pipeline"); }
+  lens->pipeline = pipeline;
+  return BZ_OK;
+}
+
+int bz_lens_check(bz_lens *lens) {
+  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+  if(lens->d_wave == nullptr) { return BZ_OK; }
+  BZ_CUDA(cudaSetDevice(lens->device));
+  uint32_t flag = 0u;
+  BZ_CUDA(cudaMemcpy(&flag, lens->wave.counters + 3, sizeof(flag), cudaMemcpyDeviceToHost));      // (synchronises with the work in flight)
+  if(flag != 0u) {
+    BZ_CUDA(cudaMemset(lens->wave.counters + 3, 0, sizeof(flag)));
+    return bz_fail(BZ_ERR_OVERFLOW, "candidate list of the wavefront pipeline overflowed (more than 4 stage-A survivors per ray over a whole chunk): the last frames are incomplete; "
+                                    "render with bz_lens_set_pipeline(lens, BZ_PIPELINE_PERSISTENT)");
+  }
   return BZ_OK;
 }
 
@@ -386,6 +413,64 @@ static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<u
   return true;
 }
 
+// ---- RENDER through the wavefront pipeline (csrc/bz_wave.cu) ----
+// The tiles of the job (desc.tile_count of them, in hand-out order) are cut into chunks of at most BZ_WAVE_RAYS ray slots; a
+// chunk goes through walk + stage A, stage B and resolve once per surface crossing.  The buffers belong to the handle and are
+// sized for the largest chunk so far: 36 bytes per ray slot, 52 bytes per candidate, BZ_WAVE_CANDS candidates per ray slot.
+#define BZ_WAVE_RAYS   (4u << 20)
+#define BZ_WAVE_MIN_RAYS (1ull << 20)      // BZ_PIPELINE_AUTO: RENDER jobs with at least this many rays on lens tiles take the wavefront pipeline
+#define BZ_WAVE_CANDS  4u
+
+static int bz_wave_reserve(bz_lens *lens, uint32_t ray_cap) {
+  uint64_t const cand_cap = std::max<uint64_t>((uint64_t)ray_cap * BZ_WAVE_CANDS, 1u << 16);
+  auto round = [](uint64_t bytes) { return (bytes + 255u) / 256u * 256u; };
+  uint64_t const sizes[8] = { round((uint64_t)ray_cap * 16u), round((uint64_t)ray_cap * 16u), round((uint64_t)ray_cap * 4u), round(cand_cap * 8u), round(cand_cap * 4u),
+                              round(cand_cap * 8u), round(cand_cap * 32u), 256u };
+  uint64_t total = 0u;
+  for(uint64_t size : sizes) { total += size; }
+  if(lens->d_wave == nullptr || lens->wave_bytes < total || lens->wave.ray_cap < ray_cap) {
+    if(lens->d_wave != nullptr) { BZ_CUDA(cudaFree(lens->d_wave)); lens->d_wave = nullptr; lens->wave_bytes = 0u; }
+    BZ_CUDA(cudaMalloc(&lens->d_wave, total));
+    BZ_CUDA(cudaMemset(lens->d_wave, 0, total));
+    lens->wave_bytes = total;
+    char *at = (char*)lens->d_wave;
+    lens->wave.ray_a = (float4*)at; at += sizes[0];
+    lens->wave.ray_b = (float4*)at; at += sizes[1];
+    lens->wave.head = (uint32_t*)at; at += sizes[2];
+    lens->wave.cand = (uint2*)at; at += sizes[3];
+    lens->wave.cand_next = (uint32_t*)at; at += sizes[4];
+    lens->wave.cand_key = (unsigned long long*)at; at += sizes[5];
+    lens->wave.cand_pay = (float4*)at; at += sizes[6];
+    lens->wave.counters = (uint32_t*)at;
+    lens->wave.ray_cap = ray_cap;
+    lens->wave.cand_cap = (uint32_t)std::min<uint64_t>(cand_cap, 0xfffffff0ull);
+  }
+  return BZ_OK;
+}
+
+static int bz_run_wave(bz_lens *lens, const bz_job &desc, cudaStream_t stream) {
+  uint32_t const packets_per_tile = (desc.tile_rays + 31u) / 32u;
+  uint32_t const tile_slots = packets_per_tile * 32u;
+  uint32_t const tiles = (uint32_t)desc.tile_count;
+  uint32_t const chunk_tiles = std::max<uint32_t>(1u, std::min<uint32_t>(tiles, BZ_WAVE_RAYS / tile_slots));
+  int rc = bz_wave_reserve(lens, chunk_tiles * tile_slots);
+  if(rc != BZ_OK) { return rc; }
+  uint32_t const levels = std::max<uint32_t>(1u, desc.scene.max_crossings);
+  for(uint32_t first = 0u; first < tiles; first += chunk_tiles) {
+    bz_wave wave = lens->wave;
+    wave.first_tile = first;
+    wave.tile_count = std::min(chunk_tiles, tiles - first);
+    wave.packets_per_tile = packets_per_tile;
+    for(uint32_t level = 0u; level < levels; ++level) {
+      wave.level = level;
+      if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_wave_pass_fast(lens->tables, desc, wave, lens->sm_count, stream)); }
+      else { BZ_CUDA(bz_launch_wave_pass(lens->tables, desc, wave, lens->sm_count, stream)); }
+      lens->launches += 3u;
+    }
+  }
+  return BZ_OK;
+}
+
 static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
   BZ_CUDA(cudaSetDevice(lens->device));
   lens->timed = false;
@@ -481,7 +566,14 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
     bz_tables tables = lens->tables;
     if(lens->mode == BZ_MODE_LANES) { tables.packet_count = 0u; }
     if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, lens->d_tiles + desc.tile_count, sky_count, stream)); ++lens->launches; }
-    if(grid != 0) {
+    // RENDER with enough rays on the lens: the wavefront pipeline; small frames and the batch jobs: the persistent kernel
+    bool const wavefront = job == BZ_JOB_RENDER && lens->mode != BZ_MODE_LANES && grid != 0
+                        && (lens->pipeline == BZ_PIPELINE_WAVEFRONT || (lens->pipeline == BZ_PIPELINE_AUTO && desc.tile_count * desc.tile_rays >= BZ_WAVE_MIN_RAYS));
+    if(wavefront) {
+      int rc = bz_run_wave(lens, desc, stream);
+      if(rc != BZ_OK) { return rc; }
+    }
+    else if(grid != 0) {
       if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_warp_trace_fast(job, tables, desc, grid, stream)); }
       else { BZ_CUDA(bz_launch_warp_trace(job, tables, desc, grid, stream)); }
       ++lens->launches;
@@ -683,7 +775,7 @@ int bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene
     for(size_t i = 0u; i < sizeof(bz_stats) / sizeof(uint64_t); ++i) { acc[i] += add[i]; }
   }
   BZ_CUDA(cudaStreamSynchronize(0));
-  return BZ_OK;
+  return bz_lens_check(lens);
 }
 
 int bz_last_kernel_ms(bz_lens *lens, float *out_ms) {

@@ -99,6 +99,31 @@ struct bz_job {
   unsigned long long *stats;      // 9 counters in bz_stats order, accumulated; nullable
 };
 
+// ---- wavefront pipeline of a RENDER job (csrc/bz_wave.cu) ----
+// The tiles of the job that can meet the lens are cut into chunks; a chunk goes, once per surface crossing, through three
+// kernels that talk through these buffers (sized per context, L2 / HBM resident):
+//   bz_wave_walk_kernel     per packet of 32 rays: ray generation (first crossing) or reload, packet walk, stage A; the
+//                           survivors become candidates (ray slot, patch) appended to `cand`, chained per ray through
+//                           `head` / `cand_next`
+//   bz_wave_eval_kernel     per candidate: stage B (and the one follow-side hop); result key + hit record per candidate
+//   bz_wave_resolve_kernel  per ray: nearest result of its chain, Snell, next ray or shading
+struct bz_wave {
+  float4   *ray_a;          // [ray_cap]      start.xyz, dir.x
+  float4   *ray_b;          // [ray_cap]      dir.y, dir.z, local pixel index (bits), state (bits): bit 0 live, 1-2 expected status, 4.. crossings
+  uint32_t *head;           // [ray_cap]      1 + index of the newest candidate of the ray's current call, 0 = none
+  uint2    *cand;           // [cand_cap]     (ray slot, patch)
+  uint32_t *cand_next;      // [cand_cap]     1 + index of the ray's next candidate, 0 = end of the chain
+  unsigned long long *cand_key;   // [cand_cap]   (distance key, loop index) of the candidate's hit, BZ_KEY_NONE without one
+  float4   *cand_pay;       // [2 * cand_cap] point.xyz, cos incidence | normal.xyz, evaluated patch (bits)
+  uint32_t *counters;       // [0] next packet of the walk  [1] candidates of this pass  [2] next batch of the evaluation
+                            // [3] sticky: the candidate buffer overflowed (the frame is incomplete, the next call reports it)
+  uint32_t  ray_cap, cand_cap;
+  uint32_t  first_tile;     // chunk = tiles [first_tile, first_tile + tile_count) of the job's tile order
+  uint32_t  tile_count;
+  uint32_t  packets_per_tile;
+  uint32_t  level;          // 0: the walk kernel generates the primary rays
+};
+
 #define BZ_RAY_PASSED 0xffffffffu     // illumination mode: patch key of an emitter ray that passed beside the lens (bz_pass_kernel)
 
 // UniformHemisphere belt table (reference/hostUtil.cpp:8-13), passed to the emission kernel by value

@@ -29,6 +29,7 @@ extern "C" {
 #define BZ_ERR_CUDA          -2   /* CUDA runtime error, see bz_last_error() */
 #define BZ_ERR_NO_DEVICE     -3   /* no usable CUDA device: there is no CPU path */
 #define BZ_ERR_PREPROCESS    -4   /* mesh preprocessing threw (e.g. "Vertex on edge detected.", reference/mesh.cpp:204) */
+#define BZ_ERR_OVERFLOW      -5   /* a device-side work list overflowed (bz_lens_check) */
 
 /* RefractionResult, reference/bezierLens.h:7-11 */
 #define BZ_STATUS_NONE        0u
@@ -164,6 +165,18 @@ int  bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refra
 int  bz_lens_destroy(bz_lens *lens);
 int  bz_lens_set_mode(bz_lens *lens, uint32_t mode);
 int  bz_lens_patch_count(const bz_lens *lens, uint32_t *out_count);
+/* How bz_render* runs the tiles that can meet the lens (BZ_MODE_CULLED / BZ_MODE_FAST; the results are the same bits):
+ *   BZ_PIPELINE_PERSISTENT  one persistent warp-scheduled kernel does walk, stage A, stage B and resolve (csrc/bz_trace.cu)
+ *   BZ_PIPELINE_WAVEFRONT   three kernels per surface crossing over global ray / candidate lists (csrc/bz_wave.cu)
+ *   BZ_PIPELINE_AUTO        wavefront for frames with at least 2^20 rays on lens tiles, else persistent (the default)
+ * The batch entry points (bz_refract_batch, bz_intersect_batch, bz_trace_to_target) always use the persistent kernel. */
+#define BZ_PIPELINE_AUTO        0u
+#define BZ_PIPELINE_PERSISTENT  1u
+#define BZ_PIPELINE_WAVEFRONT   2u
+int  bz_lens_set_pipeline(bz_lens *lens, uint32_t pipeline);
+/* Synchronises with the work in flight on the handle and reports (once) a device-side overflow of the wavefront pipeline's
+ * candidate list as BZ_ERR_OVERFLOW; the *_host render calls do this themselves. */
+int  bz_lens_check(bz_lens *lens);
 
 /* BezierLens::refract over a batch  -- reference/bezierLens.h:27, bezierLens.cpp:4-34.
  * start/dir: n x 3 floats (dir must be unit length, as Ray::Ray leaves it, 3dGeomUtil.h:176-178).

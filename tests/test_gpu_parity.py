@@ -91,16 +91,21 @@ def test_render_pixel_exact_vs_reference(bz, oracle_built, name, w, h, strata, c
     rcam, rscene = bzref.make_camera(w, h, **cam_args), bzref.make_scene(bg_x=float(hi[0]) + 12.0, max_crossings=crossings)
     ref_rgba, ref_stats, rays = bzref.RefLens(ri, bezier).render(rcam, rscene, threads=8)
     cam, scene = bz.make_camera(w, h, **cam_args), bz.make_scene(bg_x=float(hi[0]) + 12.0, max_crossings=crossings)
-    for mode in (bz.MODE_CULLED, bz.MODE_LANES, bz.MODE_BRUTE):
-        rgba, stats = bz.BezierLens(ri, patches).set_mode(mode).render(cam, scene)
-        assert np.array_equal(rgba, ref_rgba), "%d of %d pixels differ" % (int((rgba != ref_rgba).any(-1).sum()), w * h)
+    counts = {}
+    for mode, pipeline in ((bz.MODE_CULLED, bz.PIPELINE_PERSISTENT), (bz.MODE_CULLED, bz.PIPELINE_WAVEFRONT), (bz.MODE_LANES, bz.PIPELINE_AUTO), (bz.MODE_BRUTE, bz.PIPELINE_AUTO)):
+        rgba, stats = bz.BezierLens(ri, patches).set_mode(mode).set_pipeline(pipeline).render(cam, scene)
+        assert np.array_equal(rgba, ref_rgba), "mode %d pipeline %d: %d of %d pixels differ" % (mode, pipeline, int((rgba != ref_rgba).any(-1).sum()), w * h)
         got, want = stats.as_dict(), ref_stats.as_dict()
         for key in ("primary_rays", "refract_calls", "entered", "exited", "lost"):
             assert got[key] == want[key], key
         if mode == bz.MODE_CULLED:      # camera rays go through the warp-cooperative walk (a coarse image of a fine mesh falls back in part)
             assert stats.packet_walks > 0 and stats.lane_walk_calls < stats.refract_calls
-        if mode == bz.MODE_LANES:
-            assert stats.packet_walks == 0 and stats.lane_walk_calls == stats.refract_calls
+            counts[pipeline] = got
+    # the two pipelines do the same work: same stage-A tests, stage-B evaluations, Snell blocks, walks
+    for key in ("stage_a", "stage_b", "snell", "packet_walks", "lane_walk_calls", "packet_nodes", "node_visits"):
+        assert counts[bz.PIPELINE_PERSISTENT][key] == counts[bz.PIPELINE_WAVEFRONT][key], key
+    stats = bz.BezierLens(ri, patches).set_mode(bz.MODE_LANES).render(cam, scene)[1]
+    assert stats.packet_walks == 0 and stats.lane_walk_calls == stats.refract_calls
     assert ref_stats.entered > 100
 
 
@@ -121,8 +126,8 @@ def test_render_sky_tiles_pixel_exact(bz, oracle_built, label, cam_args, plans):
     rcam, rscene = bzref.make_camera(w, h, strata=strata, **cam_args), bzref.make_scene(bg_x=30.0, max_crossings=2)
     ref_rgba, ref_stats, _ = bzref.RefLens(1.3, bezier).render(rcam, rscene, threads=8)
     cam, scene = bz.make_camera(w, h, strata=strata, **cam_args), bz.make_scene(bg_x=30.0, max_crossings=2)
-    for mode in (bz.MODE_CULLED, bz.MODE_LANES):
-        lens = bz.BezierLens(1.3, patches).set_mode(mode)
+    for mode, pipeline in ((bz.MODE_CULLED, bz.PIPELINE_PERSISTENT), (bz.MODE_CULLED, bz.PIPELINE_WAVEFRONT), (bz.MODE_LANES, bz.PIPELINE_AUTO)):
+        lens = bz.BezierLens(1.3, patches).set_mode(mode).set_pipeline(pipeline)
         for again in range(2):                                  # the second frame reuses the kept tile plan
             rgba, stats = lens.render(cam, scene)
             assert np.array_equal(rgba, ref_rgba), "%s: %d of %d pixels differ" % (label, int((rgba != ref_rgba).any(-1).sum()), w * h)
@@ -131,7 +136,8 @@ def test_render_sky_tiles_pixel_exact(bz, oracle_built, label, cam_args, plans):
                 assert got[key] == want[key], (label, key)
         launches = lens.last_kernel_launches()
         if mode == bz.MODE_CULLED and plans:
-            assert launches == (3 if ref_stats.entered > 0 else 2), label        # sky + trace + resolve; no trace when nothing can meet the lens
+            trace = 1 if pipeline == bz.PIPELINE_PERSISTENT else 3 * 2                # one persistent kernel, or walk + eval + resolve per crossing
+            assert launches == (2 + trace if ref_stats.entered > 0 else 2), label    # sky + trace + resolve; no trace when nothing can meet the lens
         else:
             assert launches == 2, label
         # a band of the frame and a moved camera make a new plan
