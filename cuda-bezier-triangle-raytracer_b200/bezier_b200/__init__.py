@@ -132,6 +132,9 @@ SIGNATURES = {
     "bz_lens_patch_count": (_int, [_vp, C.POINTER(_u32)]),
     "bz_lens_set_pipeline": (_int, [_vp, _u32]),
     "bz_lens_check": (_int, [_vp]),
+    "bz_lens_set_wave_chunk": (_int, [_vp, _u32]),
+    "bz_lens_release_stream": (_int, [_vp, _vp]),
+    "bz_last_plan_ms": (_int, [_vp, C.POINTER(_f)]),
     "bz_lens_info": (_int, [_vp, C.POINTER(_u32 * 4)]),
     "bz_refract_batch": (_int, [_vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp]),
     "bz_refract_batch_host": (_int, [_vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
@@ -428,6 +431,10 @@ class BezierLens:
         _check(self.lib.bz_lens_set_pipeline(self.h, pipeline))
         return self
 
+    def set_wave_chunk(self, ray_slots):
+        _check(self.lib.bz_lens_set_wave_chunk(self.h, ray_slots))
+        return self
+
     def check(self):
         """synchronise and raise if a device-side work list overflowed since the last check"""
         _check(self.lib.bz_lens_check(self.h))
@@ -441,6 +448,14 @@ class BezierLens:
         ms = _f(0.0)
         _check(self.lib.bz_last_kernel_ms(self.h, C.byref(ms)))
         return ms.value
+
+    def last_plan_ms(self):
+        ms = _f(0.0)
+        _check(self.lib.bz_last_plan_ms(self.h, C.byref(ms)))
+        return ms.value
+
+    def release_stream(self, stream):
+        _check(self.lib.bz_lens_release_stream(self.h, C.c_void_p(int(stream))))
 
     def last_kernel_launches(self):
         count = _u32(0)

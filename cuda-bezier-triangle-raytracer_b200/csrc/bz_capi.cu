@@ -8,6 +8,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
+#include <mutex>
 #include <string>
 #include <vector>
 #include "bz_capi.h"
@@ -46,12 +48,20 @@ int bz_fail(int code, const std::string &text) {
 #define BZ_CUDA(call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) { \
   return bz_fail(BZ_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while(0)
 
-struct bz_lens {
-  int        device;
-  int        sm_count;
-  uint32_t   mode;
-  bz_tables  tables;
-  float4    *d_cull, *d_newton, *d_leaf, *d_pairs, *d_nodes, *d_packet;
+#define BZ_WAVE_RAYS   (4u << 20)
+#define BZ_WAVE_MIN_RAYS (1ull << 20)      // BZ_PIPELINE_AUTO: RENDER jobs with at least this many rays on lens tiles take the wavefront pipeline
+#define BZ_WAVE_CANDS  4u
+
+struct bz_lens;
+
+// Working set of the calls a lens gets on ONE stream: everything a call writes besides the caller's buffers.  The tables of
+// the lens are read-only, so calls on different streams (each with its own context) may overlap -- BezierLens::refract is
+// const and re-entrant in the reference (bezierLens.h:27).  A call holds `busy` while it enqueues its work.
+struct bz_context {
+  bz_lens     *lens;
+  cudaStream_t stream;                // the stream this context serves; host contexts: a non-blocking stream of their own
+  bool         owns_stream;
+  std::mutex   busy;
   unsigned long long *d_counter;      // work counter of the persistent kernel
   uint32_t  *d_accum;                 // render scratch: one u32 per pixel of the largest band so far
   size_t     accum_pixels;
@@ -60,30 +70,48 @@ struct bz_lens {
   void      *d_scratch;               // *_host staging
   size_t     scratch_bytes;
   cudaEvent_t ev_begin, ev_end;
-  cudaStream_t last_stream;
   bool       timed;
-  uint32_t   bvh_depth;
-  // RENDER: which tiles of a frame can meet the lens (bz_plan_tiles)
-  std::vector<float> outline;         // up to BZ_OUTLINE_BOXES boxes of the cull hierarchy that cover every patch: lo.xyz hi.xyz each
+  // RENDER: which tiles of a frame can meet the lens (bz_plan_tiles); the plan of the last frame is kept
   struct {
     bool      valid;
+    uint32_t  mode;
     bz_camera camera;
     uint32_t  row0, rows, stripe_rows, rank, ranks, side;
     uint32_t  lens_count, sky_count;  // d_tiles = lens tiles in hand-out order, then sky tiles
   } plan;
   uint32_t  *d_tiles;
   size_t     tiles_capacity;
-  cudaEvent_t ev_plan;                // the upload of d_tiles (a call on another stream waits for it)
-  cudaStream_t plan_stream;
+  uint32_t  *h_tiles;                 // pinned staging of the tile list (the upload is a true asynchronous copy)
+  size_t     h_tiles_capacity;
+  cudaEvent_t ev_tiles;               // the last upload out of h_tiles has been consumed
+  double     plan_ms;                 // host time of the most recent call's bz_plan_tiles + upload (0: the kept plan was used)
   uint32_t   launches;                // kernels of the most recent call
   // RENDER, wavefront pipeline (csrc/bz_wave.cu): ray slots and candidate list of one chunk of tiles
-  uint32_t   pipeline;                // BZ_PIPELINE_*
   bz_wave    wave;
   void      *d_wave;                  // one allocation behind the pointers of `wave`
   size_t     wave_bytes;
 };
 
+struct bz_lens {
+  int        device;
+  int        sm_count;
+  uint32_t   mode;
+  uint32_t   pipeline;                // BZ_PIPELINE_*
+  uint32_t   wave_chunk;              // ray slots per chunk of the wavefront pipeline
+  bz_tables  tables;
+  float4    *d_cull, *d_newton, *d_leaf, *d_pairs, *d_nodes, *d_packet;
+  uint32_t   bvh_depth;
+  std::vector<float> outline;         // up to BZ_OUTLINE_BOXES boxes of the cull hierarchy that cover every patch: lo.xyz hi.xyz each
+  std::mutex lock;                    // guards the two lists below
+  std::vector<bz_context*> contexts;  // one per stream seen so far (bz_lens_release_stream drops one)
+  std::vector<bz_context*> idle_host; // contexts of finished *_host calls, waiting for the next one
+};
+
+// the context of the calling thread's most recent call (bz_last_kernel_ms / bz_last_kernel_launches)
+static thread_local bz_context *gLastContext = nullptr;
+
 static void bz_outline_boxes(const bz_bvh &bvh, std::vector<float> &out);
+static void bz_context_free(bz_context *ctx);
 
 static int bz_check_device(int device) {
   int count = 0;
@@ -95,6 +123,73 @@ static int bz_check_device(int device) {
   if(device < 0 || device >= count) { return bz_fail(BZ_ERR_INVALID, "device index out of range"); }
   return BZ_OK;
 }
+
+// ---- contexts ----
+static void bz_context_free(bz_context *ctx) {
+  if(ctx == nullptr) { return; }
+  cudaFree(ctx->d_counter); cudaFree(ctx->d_accum); cudaFree(ctx->d_scratch); cudaFree(ctx->d_illum); cudaFree(ctx->d_tiles); cudaFree(ctx->d_wave);
+  if(ctx->h_tiles != nullptr) { cudaFreeHost(ctx->h_tiles); }
+  if(ctx->ev_begin) { cudaEventDestroy(ctx->ev_begin); }
+  if(ctx->ev_end) { cudaEventDestroy(ctx->ev_end); }
+  if(ctx->ev_tiles) { cudaEventDestroy(ctx->ev_tiles); }
+  if(ctx->owns_stream && ctx->stream != nullptr) { cudaStreamDestroy(ctx->stream); }
+  delete ctx;
+}
+
+static int bz_context_new(bz_lens *lens, cudaStream_t stream, bool own_stream, bz_context **out) {
+  BZ_CUDA(cudaSetDevice(lens->device));
+  bz_context *ctx = new bz_context();      // (value-initialised: every plain member is zero)
+  ctx->lens = lens;
+  ctx->stream = stream;
+  cudaError_t e = cudaSuccess;
+  if(own_stream) {
+    e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    ctx->owns_stream = (e == cudaSuccess);
+  }
+  if(e == cudaSuccess) { e = cudaMalloc((void**)&ctx->d_counter, 64u); }
+  if(e == cudaSuccess) { e = cudaEventCreate(&ctx->ev_begin); }
+  if(e == cudaSuccess) { e = cudaEventCreate(&ctx->ev_end); }
+  if(e == cudaSuccess) { e = cudaEventCreateWithFlags(&ctx->ev_tiles, cudaEventDisableTiming); }
+  if(e != cudaSuccess) {
+    std::string const text = cudaGetErrorString(e);
+    bz_context_free(ctx);
+    return bz_fail(BZ_ERR_CUDA, "bz_context_new: " + text);
+  }
+  *out = ctx;
+  return BZ_OK;
+}
+
+// the context that serves `stream` on this lens (made on first use)
+static int bz_context_for(bz_lens *lens, cudaStream_t stream, bz_context **out) {
+  std::lock_guard<std::mutex> hold(lens->lock);
+  for(bz_context *ctx : lens->contexts) {
+    if(ctx->stream == stream) { *out = ctx; return BZ_OK; }
+  }
+  int rc = bz_context_new(lens, stream, false, out);
+  if(rc == BZ_OK) { lens->contexts.push_back(*out); }
+  return rc;
+}
+
+// a *_host call: takes an idle host context (own non-blocking stream) or makes one, gives it back when it ends, so that
+// host calls from any number of threads run side by side on one lens
+struct bz_host_call {
+  bz_lens *lens;
+  bz_context *ctx;
+  int rc;
+  explicit bz_host_call(bz_lens *aLens) : lens(aLens), ctx(nullptr), rc(BZ_OK) {
+    {
+      std::lock_guard<std::mutex> hold(lens->lock);
+      if(!lens->idle_host.empty()) { ctx = lens->idle_host.back(); lens->idle_host.pop_back(); }
+    }
+    if(ctx == nullptr) { rc = bz_context_new(lens, nullptr, true, &ctx); }
+  }
+  ~bz_host_call() {
+    if(ctx != nullptr) {
+      std::lock_guard<std::mutex> hold(lens->lock);
+      lens->idle_host.push_back(ctx);
+    }
+  }
+};
 
 extern "C" {
 
@@ -117,11 +212,10 @@ uint32_t bz_sizeof_stats(void) { return (uint32_t)sizeof(bz_stats); }
 int bz_lens_destroy(bz_lens *lens) {
   if(lens == nullptr) { return BZ_OK; }
   cudaSetDevice(lens->device);
+  for(bz_context *ctx : lens->contexts) { bz_context_free(ctx); }
+  for(bz_context *ctx : lens->idle_host) { bz_context_free(ctx); }
+  if(gLastContext != nullptr && gLastContext->lens == lens) { gLastContext = nullptr; }
   cudaFree(lens->d_cull); cudaFree(lens->d_newton); cudaFree(lens->d_leaf); cudaFree(lens->d_pairs); cudaFree(lens->d_nodes); cudaFree(lens->d_packet);
-  cudaFree(lens->d_counter); cudaFree(lens->d_accum); cudaFree(lens->d_scratch); cudaFree(lens->d_illum); cudaFree(lens->d_tiles); cudaFree(lens->d_wave);
-  if(lens->ev_begin) { cudaEventDestroy(lens->ev_begin); }
-  if(lens->ev_plan) { cudaEventDestroy(lens->ev_plan); }
-  if(lens->ev_end) { cudaEventDestroy(lens->ev_end); }
   delete lens;
   return BZ_OK;
 }
@@ -171,6 +265,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   bz_lens *lens = new bz_lens();      // (value-initialised: every plain member is zero)
   lens->device = device;
   lens->mode = BZ_MODE_CULLED;
+  lens->wave_chunk = BZ_WAVE_RAYS;
   lens->bvh_depth = bvh.depth;
   bz_outline_boxes(bvh, lens->outline);
   cudaDeviceProp prop;
@@ -204,10 +299,6 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   }
   if(e == cudaSuccess) { e = upload(bvh.nodes, &lens->d_nodes); }
   if(e == cudaSuccess) { e = upload(bvh.packet_nodes, &lens->d_packet); }
-  if(e == cudaSuccess) { e = cudaMalloc((void**)&lens->d_counter, 64u); }
-  if(e == cudaSuccess) { e = cudaEventCreate(&lens->ev_begin); }
-  if(e == cudaSuccess) { e = cudaEventCreateWithFlags(&lens->ev_plan, cudaEventDisableTiming); }
-  if(e == cudaSuccess) { e = cudaEventCreate(&lens->ev_end); }
   if(e != cudaSuccess) {
     std::string text = cudaGetErrorString(e);
     bz_lens_destroy(lens);
@@ -244,17 +335,54 @@ int bz_lens_set_pipeline(bz_lens *lens, uint32_t pipeline) {
   return BZ_OK;
 }
 
+int bz_lens_set_wave_chunk(bz_lens *lens, uint32_t ray_slots) {
+  if(lens == nullptr || ray_slots < 1024u || ray_slots > (1u << 26)) { return bz_fail(BZ_ERR_INVALID, "bad lens or chunk size (1024 .. 2^26 ray slots)"); }
+  lens->wave_chunk = ray_slots;
+  return BZ_OK;
+}
+
 int bz_lens_check(bz_lens *lens) {
   if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
-  if(lens->d_wave == nullptr) { return BZ_OK; }
   BZ_CUDA(cudaSetDevice(lens->device));
-  uint32_t flag = 0u;
-  BZ_CUDA(cudaMemcpy(&flag, lens->wave.counters + 3, sizeof(flag), cudaMemcpyDeviceToHost));      // (synchronises with the work in flight)
-  if(flag != 0u) {
-    BZ_CUDA(cudaMemset(lens->wave.counters + 3, 0, sizeof(flag)));
+  std::vector<bz_context*> all;
+  {
+    std::lock_guard<std::mutex> hold(lens->lock);
+    all = lens->contexts;
+    all.insert(all.end(), lens->idle_host.begin(), lens->idle_host.end());
+  }
+  bool overflowed = false;
+  for(bz_context *ctx : all) {
+    if(ctx->d_wave == nullptr) { continue; }
+    std::lock_guard<std::mutex> hold(ctx->busy);
+    uint32_t flag = 0u;
+    BZ_CUDA(cudaMemcpyAsync(&flag, ctx->wave.counters + 3, sizeof(flag), cudaMemcpyDeviceToHost, ctx->stream));
+    BZ_CUDA(cudaStreamSynchronize(ctx->stream));      // (waits for the work in flight on that stream)
+    if(flag != 0u) {
+      BZ_CUDA(cudaMemsetAsync(ctx->wave.counters + 3, 0, sizeof(flag), ctx->stream));
+      overflowed = true;
+    }
+  }
+  if(overflowed) {
     return bz_fail(BZ_ERR_OVERFLOW, "candidate list of the wavefront pipeline overflowed (more than 4 stage-A survivors per ray over a whole chunk): the last frames are incomplete; "
                                     "render with bz_lens_set_pipeline(lens, BZ_PIPELINE_PERSISTENT)");
   }
+  return BZ_OK;
+}
+
+int bz_lens_release_stream(bz_lens *lens, void *stream) {
+  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+  bz_context *found = nullptr;
+  {
+    std::lock_guard<std::mutex> hold(lens->lock);
+    for(size_t i = 0u; i < lens->contexts.size(); ++i) {
+      if(lens->contexts[i]->stream == (cudaStream_t)stream) { found = lens->contexts[i]; lens->contexts.erase(lens->contexts.begin() + (long)i); break; }
+    }
+  }
+  if(found == nullptr) { return BZ_OK; }
+  BZ_CUDA(cudaSetDevice(lens->device));
+  BZ_CUDA(cudaStreamSynchronize(found->stream));
+  if(gLastContext == found) { gLastContext = nullptr; }
+  bz_context_free(found);
   return BZ_OK;
 }
 
@@ -417,47 +545,47 @@ static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<u
 // The tiles of the job (desc.tile_count of them, in hand-out order) are cut into chunks of at most BZ_WAVE_RAYS ray slots; a
 // chunk goes through walk + stage A, stage B and resolve once per surface crossing.  The buffers belong to the handle and are
 // sized for the largest chunk so far: 36 bytes per ray slot, 52 bytes per candidate, BZ_WAVE_CANDS candidates per ray slot.
-#define BZ_WAVE_RAYS   (4u << 20)
-#define BZ_WAVE_MIN_RAYS (1ull << 20)      // BZ_PIPELINE_AUTO: RENDER jobs with at least this many rays on lens tiles take the wavefront pipeline
-#define BZ_WAVE_CANDS  4u
 
-static int bz_wave_reserve(bz_lens *lens, uint32_t ray_cap) {
+static int bz_wave_reserve(bz_context *ctx, uint32_t ray_cap) {
   uint64_t const cand_cap = std::max<uint64_t>((uint64_t)ray_cap * BZ_WAVE_CANDS, 1u << 16);
   auto round = [](uint64_t bytes) { return (bytes + 255u) / 256u * 256u; };
   uint64_t const sizes[8] = { round((uint64_t)ray_cap * 16u), round((uint64_t)ray_cap * 16u), round((uint64_t)ray_cap * 4u), round(cand_cap * 8u), round(cand_cap * 4u),
                               round(cand_cap * 8u), round(cand_cap * 32u), 256u };
   uint64_t total = 0u;
   for(uint64_t size : sizes) { total += size; }
-  if(lens->d_wave == nullptr || lens->wave_bytes < total || lens->wave.ray_cap < ray_cap) {
-    if(lens->d_wave != nullptr) { BZ_CUDA(cudaFree(lens->d_wave)); lens->d_wave = nullptr; lens->wave_bytes = 0u; }
-    BZ_CUDA(cudaMalloc(&lens->d_wave, total));
-    BZ_CUDA(cudaMemset(lens->d_wave, 0, total));
-    lens->wave_bytes = total;
-    char *at = (char*)lens->d_wave;
-    lens->wave.ray_a = (float4*)at; at += sizes[0];
-    lens->wave.ray_b = (float4*)at; at += sizes[1];
-    lens->wave.head = (uint32_t*)at; at += sizes[2];
-    lens->wave.cand = (uint2*)at; at += sizes[3];
-    lens->wave.cand_next = (uint32_t*)at; at += sizes[4];
-    lens->wave.cand_key = (unsigned long long*)at; at += sizes[5];
-    lens->wave.cand_pay = (float4*)at; at += sizes[6];
-    lens->wave.counters = (uint32_t*)at;
-    lens->wave.ray_cap = ray_cap;
-    lens->wave.cand_cap = (uint32_t)std::min<uint64_t>(cand_cap, 0xfffffff0ull);
+  if(ctx->d_wave == nullptr || ctx->wave_bytes < total || ctx->wave.ray_cap < ray_cap) {
+    if(ctx->d_wave != nullptr) { BZ_CUDA(cudaFree(ctx->d_wave)); ctx->d_wave = nullptr; ctx->wave_bytes = 0u; }
+    BZ_CUDA(cudaMalloc(&ctx->d_wave, total));
+    BZ_CUDA(cudaMemset(ctx->d_wave, 0, total));
+    ctx->wave_bytes = total;
+    char *at = (char*)ctx->d_wave;
+    ctx->wave.ray_a = (float4*)at; at += sizes[0];
+    ctx->wave.ray_b = (float4*)at; at += sizes[1];
+    ctx->wave.head = (uint32_t*)at; at += sizes[2];
+    ctx->wave.cand = (uint2*)at; at += sizes[3];
+    ctx->wave.cand_next = (uint32_t*)at; at += sizes[4];
+    ctx->wave.cand_key = (unsigned long long*)at; at += sizes[5];
+    ctx->wave.cand_pay = (float4*)at; at += sizes[6];
+    ctx->wave.counters = (uint32_t*)at;
+    ctx->wave.ray_cap = ray_cap;
+    ctx->wave.cand_cap = (uint32_t)std::min<uint64_t>(cand_cap, 0xfffffff0ull);
   }
   return BZ_OK;
 }
 
-static int bz_run_wave(bz_lens *lens, const bz_job &desc, cudaStream_t stream) {
+static int bz_run_wave(bz_context *ctx, const bz_job &desc) {
+  bz_lens *lens = ctx->lens;
+  cudaStream_t const stream = ctx->stream;
   uint32_t const packets_per_tile = (desc.tile_rays + 31u) / 32u;
   uint32_t const tile_slots = packets_per_tile * 32u;
   uint32_t const tiles = (uint32_t)desc.tile_count;
-  uint32_t const chunk_tiles = std::max<uint32_t>(1u, std::min<uint32_t>(tiles, BZ_WAVE_RAYS / tile_slots));
-  int rc = bz_wave_reserve(lens, chunk_tiles * tile_slots);
+  uint32_t const chunk_tiles = std::max<uint32_t>(1u, std::min<uint32_t>(tiles, lens->wave_chunk / tile_slots));
+  int rc = bz_wave_reserve(ctx, chunk_tiles * tile_slots);
   if(rc != BZ_OK) { return rc; }
   uint32_t const levels = std::max<uint32_t>(1u, desc.scene.max_crossings);
+  BZ_CUDA(cudaMemsetAsync(ctx->wave.counters, 0, 3u * sizeof(uint32_t), stream));      // (the kernels leave them zero; a failed launch may not)
   for(uint32_t first = 0u; first < tiles; first += chunk_tiles) {
-    bz_wave wave = lens->wave;
+    bz_wave wave = ctx->wave;
     wave.first_tile = first;
     wave.tile_count = std::min(chunk_tiles, tiles - first);
     wave.packets_per_tile = packets_per_tile;
@@ -465,23 +593,27 @@ static int bz_run_wave(bz_lens *lens, const bz_job &desc, cudaStream_t stream) {
       wave.level = level;
       if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_wave_pass_fast(lens->tables, desc, wave, lens->sm_count, stream)); }
       else { BZ_CUDA(bz_launch_wave_pass(lens->tables, desc, wave, lens->sm_count, stream)); }
-      lens->launches += 3u;
+      ctx->launches += 3u;
     }
   }
   return BZ_OK;
 }
 
-static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
+static int bz_run(bz_context *ctx, int job, bz_job &desc) {
+  bz_lens *lens = ctx->lens;
+  cudaStream_t const stream = ctx->stream;
+  gLastContext = ctx;
+  ctx->plan_ms = 0.0;
   BZ_CUDA(cudaSetDevice(lens->device));
-  lens->timed = false;
-  lens->launches = 0u;
+  ctx->timed = false;
+  ctx->launches = 0u;
   if(desc.ray_count == 0u) { return BZ_OK; }
-  BZ_CUDA(cudaMemsetAsync(lens->d_counter, 0, sizeof(unsigned long long), stream));
-  desc.next_ray = lens->d_counter;
+  BZ_CUDA(cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned long long), stream));
+  desc.next_ray = ctx->d_counter;
   desc.one = 1.0f;
   bool const brute = (lens->mode == BZ_MODE_BRUTE);
   int grid;
-  uint32_t sky_count = 0u;                // RENDER: tiles shaded by bz_sky_kernel (after the lens tiles in lens->d_tiles)
+  uint32_t sky_count = 0u;                // RENDER: tiles shaded by bz_sky_kernel (after the lens tiles in ctx->d_tiles)
   if(brute) {
     uint64_t const threads = (uint64_t)bz_trace_threads();
     uint64_t const wanted = (desc.ray_count + threads - 1u) / threads;
@@ -516,33 +648,40 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
       if(desc.tile_count >= 0xffffffffull) { return bz_fail(BZ_ERR_INVALID, "job too large"); }
       // the tiles that can meet the lens go to the trace kernel, the others to bz_sky_kernel; the plan of the last frame
       // is kept (same camera, same band: nothing to do)
-      auto &plan = lens->plan;
+      auto &plan = ctx->plan;
       bool const same = (lens->mode == BZ_MODE_CULLED || lens->mode == BZ_MODE_FAST) && plan.valid && std::memcmp(&plan.camera, &desc.camera, sizeof(bz_camera)) == 0 && plan.row0 == desc.row0 && plan.rows == desc.rows
                      && plan.stripe_rows == desc.stripe_rows && plan.rank == desc.stripe_rank && plan.ranks == desc.stripe_ranks && plan.side == side;
       if(!same) {
+        auto const t0 = std::chrono::steady_clock::now();
         plan.valid = false;
         std::vector<uint32_t> lens_tiles, sky_tiles;
         if(bz_plan_tiles(lens, desc, lens_tiles, sky_tiles)) {
           size_t const total = lens_tiles.size() + sky_tiles.size();
-          if(total > lens->tiles_capacity) {
-            if(lens->d_tiles != nullptr) { BZ_CUDA(cudaFree(lens->d_tiles)); lens->d_tiles = nullptr; lens->tiles_capacity = 0u; }
-            BZ_CUDA(cudaMalloc((void**)&lens->d_tiles, total * sizeof(uint32_t)));
-            lens->tiles_capacity = total;
+          if(total > ctx->tiles_capacity) {
+            if(ctx->d_tiles != nullptr) { BZ_CUDA(cudaFree(ctx->d_tiles)); ctx->d_tiles = nullptr; ctx->tiles_capacity = 0u; }
+            BZ_CUDA(cudaMalloc((void**)&ctx->d_tiles, total * sizeof(uint32_t)));
+            ctx->tiles_capacity = total;
           }
-          lens_tiles.insert(lens_tiles.end(), sky_tiles.begin(), sky_tiles.end());
-          BZ_CUDA(cudaMemcpyAsync(lens->d_tiles, lens_tiles.data(), total * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));     // (pageable source: staged before the call returns)
-          BZ_CUDA(cudaEventRecord(lens->ev_plan, stream));
-          lens->plan_stream = stream;
+          if(total > ctx->h_tiles_capacity) {
+            if(ctx->h_tiles != nullptr) { BZ_CUDA(cudaEventSynchronize(ctx->ev_tiles)); BZ_CUDA(cudaFreeHost(ctx->h_tiles)); ctx->h_tiles = nullptr; ctx->h_tiles_capacity = 0u; }
+            BZ_CUDA(cudaMallocHost((void**)&ctx->h_tiles, total * sizeof(uint32_t)));
+            ctx->h_tiles_capacity = total;
+          }
+          else { BZ_CUDA(cudaEventSynchronize(ctx->ev_tiles)); }      // the previous upload out of the staging buffer is done (a moving camera plans every frame)
+          std::memcpy(ctx->h_tiles, lens_tiles.data(), lens_tiles.size() * sizeof(uint32_t));
+          std::memcpy(ctx->h_tiles + lens_tiles.size(), sky_tiles.data(), sky_tiles.size() * sizeof(uint32_t));
+          BZ_CUDA(cudaMemcpyAsync(ctx->d_tiles, ctx->h_tiles, total * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+          BZ_CUDA(cudaEventRecord(ctx->ev_tiles, stream));
           plan.valid = true;
           plan.camera = desc.camera;
           plan.row0 = desc.row0; plan.rows = desc.rows; plan.stripe_rows = desc.stripe_rows; plan.rank = desc.stripe_rank; plan.ranks = desc.stripe_ranks; plan.side = side;
           plan.sky_count = (uint32_t)sky_tiles.size();
-          plan.lens_count = (uint32_t)(total - sky_tiles.size());
+          plan.lens_count = (uint32_t)lens_tiles.size();
         }
+        ctx->plan_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
       }
       if(plan.valid) {
-        if(stream != lens->plan_stream) { BZ_CUDA(cudaStreamWaitEvent(stream, lens->ev_plan, 0)); }
-        desc.tile_list = lens->d_tiles;
+        desc.tile_list = ctx->d_tiles;
         desc.tile_count = plan.lens_count;
         sky_count = plan.sky_count;
       }
@@ -560,54 +699,55 @@ static int bz_run(bz_lens *lens, int job, bz_job &desc, cudaStream_t stream) {
     else { BZ_CUDA(bz_warp_trace_occupancy(&perSm, &raysPerCta)); }
     grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * (uint64_t)std::max(perSm, 1), desc.tile_count);
   }
-  BZ_CUDA(cudaEventRecord(lens->ev_begin, stream));
-  if(brute) { BZ_CUDA(bz_launch_trace(job, true, lens->tables, desc, grid, stream)); ++lens->launches; }
+  BZ_CUDA(cudaEventRecord(ctx->ev_begin, stream));
+  if(brute) { BZ_CUDA(bz_launch_trace(job, true, lens->tables, desc, grid, stream)); ++ctx->launches; }
   else {
     bz_tables tables = lens->tables;
     if(lens->mode == BZ_MODE_LANES) { tables.packet_count = 0u; }
-    if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, lens->d_tiles + desc.tile_count, sky_count, stream)); ++lens->launches; }
+    if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, ctx->d_tiles + desc.tile_count, sky_count, stream)); ++ctx->launches; }
     // RENDER with enough rays on the lens: the wavefront pipeline; small frames and the batch jobs: the persistent kernel
     bool const wavefront = job == BZ_JOB_RENDER && lens->mode != BZ_MODE_LANES && grid != 0
                         && (lens->pipeline == BZ_PIPELINE_WAVEFRONT || (lens->pipeline == BZ_PIPELINE_AUTO && desc.tile_count * desc.tile_rays >= BZ_WAVE_MIN_RAYS));
     if(wavefront) {
-      int rc = bz_run_wave(lens, desc, stream);
+      int rc = bz_run_wave(ctx, desc);
       if(rc != BZ_OK) { return rc; }
     }
     else if(grid != 0) {
       if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_warp_trace_fast(job, tables, desc, grid, stream)); }
       else { BZ_CUDA(bz_launch_warp_trace(job, tables, desc, grid, stream)); }
-      ++lens->launches;
+      ++ctx->launches;
     }
   }
-  BZ_CUDA(cudaEventRecord(lens->ev_end, stream));
-  lens->last_stream = stream;
-  lens->timed = true;
+  BZ_CUDA(cudaEventRecord(ctx->ev_end, stream));
+  ctx->timed = true;
   return BZ_OK;
 }
 
-static int bz_scratch(bz_lens *lens, size_t bytes) {
-  if(bytes <= lens->scratch_bytes) { return BZ_OK; }
-  BZ_CUDA(cudaSetDevice(lens->device));
-  if(lens->d_scratch != nullptr) { BZ_CUDA(cudaFree(lens->d_scratch)); lens->d_scratch = nullptr; lens->scratch_bytes = 0u; }
-  BZ_CUDA(cudaMalloc(&lens->d_scratch, bytes));
-  lens->scratch_bytes = bytes;
+static int bz_scratch(bz_context *ctx, size_t bytes) {
+  if(bytes <= ctx->scratch_bytes) { return BZ_OK; }
+  BZ_CUDA(cudaSetDevice(ctx->lens->device));
+  if(ctx->d_scratch != nullptr) { BZ_CUDA(cudaFree(ctx->d_scratch)); ctx->d_scratch = nullptr; ctx->scratch_bytes = 0u; }
+  BZ_CUDA(cudaMalloc(&ctx->d_scratch, bytes));
+  ctx->scratch_bytes = bytes;
   return BZ_OK;
 }
 
-static int bz_render_common(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t rows,
-                            uint32_t stripe_rows, uint32_t rank, uint32_t ranks, uint8_t *d_rgba, bz_stats *d_stats, cudaStream_t stream) {
+static int bz_render_common(bz_context *ctx, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t rows,
+                            uint32_t stripe_rows, uint32_t rank, uint32_t ranks, uint8_t *d_rgba, bz_stats *d_stats) {
+  bz_lens *lens = ctx->lens;
+  cudaStream_t const stream = ctx->stream;
   if(camera->width == 0u || camera->height == 0u || camera->strata == 0u) { return bz_fail(BZ_ERR_INVALID, "empty camera"); }
-  if(rows == 0u) { lens->timed = false; return BZ_OK; }
+  if(rows == 0u) { ctx->timed = false; ctx->launches = 0u; gLastContext = ctx; return BZ_OK; }
   if(d_rgba == nullptr) { return bz_fail(BZ_ERR_INVALID, "d_rgba is null"); }
   BZ_CUDA(cudaSetDevice(lens->device));
   size_t const pixels = (size_t)rows * camera->width;
   if(pixels >= (1ull << 32)) { return bz_fail(BZ_ERR_INVALID, "band too large"); }
-  if(pixels > lens->accum_pixels) {
-    if(lens->d_accum != nullptr) { BZ_CUDA(cudaFree(lens->d_accum)); lens->d_accum = nullptr; lens->accum_pixels = 0u; }
-    BZ_CUDA(cudaMalloc((void**)&lens->d_accum, pixels * sizeof(uint32_t)));
-    lens->accum_pixels = pixels;
+  if(pixels > ctx->accum_pixels) {
+    if(ctx->d_accum != nullptr) { BZ_CUDA(cudaFree(ctx->d_accum)); ctx->d_accum = nullptr; ctx->accum_pixels = 0u; }
+    BZ_CUDA(cudaMalloc((void**)&ctx->d_accum, pixels * sizeof(uint32_t)));
+    ctx->accum_pixels = pixels;
   }
-  BZ_CUDA(cudaMemsetAsync(lens->d_accum, 0, pixels * sizeof(uint32_t), stream));
+  BZ_CUDA(cudaMemsetAsync(ctx->d_accum, 0, pixels * sizeof(uint32_t), stream));
   bz_job desc;
   std::memset(&desc, 0, sizeof(desc));
   desc.camera = *camera;
@@ -617,45 +757,68 @@ static int bz_render_common(bz_lens *lens, const bz_camera *camera, const bz_sce
   desc.stripe_rows = stripe_rows;
   desc.stripe_rank = rank;
   desc.stripe_ranks = ranks;
-  desc.accum = lens->d_accum;
+  desc.accum = ctx->d_accum;
   uint32_t const spp = camera->strata * camera->strata;
   desc.ray_count = (uint64_t)pixels * spp;
   desc.stats = (unsigned long long*)d_stats;
-  int rc = bz_run(lens, BZ_JOB_RENDER, desc, stream);
+  int rc = bz_run(ctx, BZ_JOB_RENDER, desc);
   if(rc != BZ_OK) { return rc; }
-  BZ_CUDA(bz_launch_resolve(lens->d_accum, d_rgba, pixels, spp, stream));
-  ++lens->launches;
+  BZ_CUDA(bz_launch_resolve(ctx->d_accum, d_rgba, pixels, spp, stream));
+  ++ctx->launches;
   return BZ_OK;
 }
 
 extern "C" {
 
-int bz_refract_batch(bz_lens *lens, const float *d_start, const float *d_dir, const uint32_t *d_expected, uint64_t n,
-                     float *d_out_start, float *d_out_dir, uint32_t *d_out_status, uint32_t *d_out_patch, void *stream) {
-  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+// the job descriptions of the two batch entry points (everything but the launch)
+static int bz_refract_job(const float *d_start, const float *d_dir, const uint32_t *d_expected, uint64_t n,
+                          float *d_out_start, float *d_out_dir, uint32_t *d_out_status, uint32_t *d_out_patch, bz_job &desc) {
   if(n != 0u && (d_start == nullptr || d_dir == nullptr || d_expected == nullptr || d_out_start == nullptr || d_out_dir == nullptr || d_out_status == nullptr)) {
     return bz_fail(BZ_ERR_INVALID, "null ray buffer");
   }
-  bz_job desc;
   std::memset(&desc, 0, sizeof(desc));
   desc.in_start = d_start; desc.in_dir = d_dir; desc.in_expected = d_expected;
   desc.out_start = d_out_start; desc.out_dir = d_out_dir; desc.out_status = d_out_status; desc.out_patch = d_out_patch;
   desc.ray_count = n;
-  return bz_run(lens, BZ_JOB_REFRACT, desc, (cudaStream_t)stream);
+  return BZ_OK;
+}
+
+static int bz_intersect_job(const float *d_start, const float *d_dir, uint64_t n, uint32_t *d_out_what, uint32_t *d_out_patch, float *d_out_distance,
+                            float *d_out_point, float *d_out_normal, float *d_out_cos, float *d_out_bary, bz_job &desc) {
+  if(n != 0u && (d_start == nullptr || d_dir == nullptr || d_out_what == nullptr)) { return bz_fail(BZ_ERR_INVALID, "null ray buffer"); }
+  std::memset(&desc, 0, sizeof(desc));
+  desc.in_start = d_start; desc.in_dir = d_dir;
+  desc.out_status = d_out_what; desc.out_patch = d_out_patch; desc.out_distance = d_out_distance; desc.out_point = d_out_point;
+  desc.out_normal = d_out_normal; desc.out_cos = d_out_cos; desc.out_bary = d_out_bary;
+  desc.ray_count = n;
+  return BZ_OK;
+}
+
+int bz_refract_batch(bz_lens *lens, const float *d_start, const float *d_dir, const uint32_t *d_expected, uint64_t n,
+                     float *d_out_start, float *d_out_dir, uint32_t *d_out_status, uint32_t *d_out_patch, void *stream) {
+  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+  bz_job desc;
+  int rc = bz_refract_job(d_start, d_dir, d_expected, n, d_out_start, d_out_dir, d_out_status, d_out_patch, desc);
+  if(rc != BZ_OK) { return rc; }
+  bz_context *ctx = nullptr;
+  rc = bz_context_for(lens, (cudaStream_t)stream, &ctx);
+  if(rc != BZ_OK) { return rc; }
+  std::lock_guard<std::mutex> hold(ctx->busy);
+  return bz_run(ctx, BZ_JOB_REFRACT, desc);
 }
 
 int bz_intersect_batch(bz_lens *lens, const float *d_start, const float *d_dir, uint64_t n,
                        uint32_t *d_out_what, uint32_t *d_out_patch, float *d_out_distance, float *d_out_point,
                        float *d_out_normal, float *d_out_cos, float *d_out_bary, void *stream) {
   if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
-  if(n != 0u && (d_start == nullptr || d_dir == nullptr || d_out_what == nullptr)) { return bz_fail(BZ_ERR_INVALID, "null ray buffer"); }
   bz_job desc;
-  std::memset(&desc, 0, sizeof(desc));
-  desc.in_start = d_start; desc.in_dir = d_dir;
-  desc.out_status = d_out_what; desc.out_patch = d_out_patch; desc.out_distance = d_out_distance; desc.out_point = d_out_point;
-  desc.out_normal = d_out_normal; desc.out_cos = d_out_cos; desc.out_bary = d_out_bary;
-  desc.ray_count = n;
-  return bz_run(lens, BZ_JOB_INTERSECT, desc, (cudaStream_t)stream);
+  int rc = bz_intersect_job(d_start, d_dir, n, d_out_what, d_out_patch, d_out_distance, d_out_point, d_out_normal, d_out_cos, d_out_bary, desc);
+  if(rc != BZ_OK) { return rc; }
+  bz_context *ctx = nullptr;
+  rc = bz_context_for(lens, (cudaStream_t)stream, &ctx);
+  if(rc != BZ_OK) { return rc; }
+  std::lock_guard<std::mutex> hold(ctx->busy);
+  return bz_run(ctx, BZ_JOB_INTERSECT, desc);
 }
 
 int bz_refract_batch_host(bz_lens *lens, const float *h_start, const float *h_dir, const uint32_t *h_expected, uint64_t n,
@@ -665,20 +828,26 @@ int bz_refract_batch_host(bz_lens *lens, const float *h_start, const float *h_di
   if(h_start == nullptr || h_dir == nullptr || h_expected == nullptr || h_out_start == nullptr || h_out_dir == nullptr || h_out_status == nullptr) {
     return bz_fail(BZ_ERR_INVALID, "null ray buffer");
   }
-  int rc = bz_scratch(lens, (size_t)n * 60u);
+  bz_host_call call(lens);
+  if(call.rc != BZ_OK) { return call.rc; }
+  bz_context *ctx = call.ctx;
+  cudaStream_t const st = ctx->stream;
+  int rc = bz_scratch(ctx, (size_t)n * 60u);
   if(rc != BZ_OK) { return rc; }
-  float *ds = (float*)lens->d_scratch, *dd = ds + n * 3u, *os = dd + n * 3u, *od = os + n * 3u;
+  float *ds = (float*)ctx->d_scratch, *dd = ds + n * 3u, *os = dd + n * 3u, *od = os + n * 3u;
   uint32_t *de = (uint32_t*)(od + n * 3u), *ost = de + n, *op = ost + n;
-  BZ_CUDA(cudaMemcpyAsync(ds, h_start, n * 12u, cudaMemcpyHostToDevice, 0));
-  BZ_CUDA(cudaMemcpyAsync(dd, h_dir, n * 12u, cudaMemcpyHostToDevice, 0));
-  BZ_CUDA(cudaMemcpyAsync(de, h_expected, n * 4u, cudaMemcpyHostToDevice, 0));
-  rc = bz_refract_batch(lens, ds, dd, de, n, os, od, ost, op, nullptr);
+  BZ_CUDA(cudaMemcpyAsync(ds, h_start, n * 12u, cudaMemcpyHostToDevice, st));
+  BZ_CUDA(cudaMemcpyAsync(dd, h_dir, n * 12u, cudaMemcpyHostToDevice, st));
+  BZ_CUDA(cudaMemcpyAsync(de, h_expected, n * 4u, cudaMemcpyHostToDevice, st));
+  bz_job desc;
+  rc = bz_refract_job(ds, dd, de, n, os, od, ost, op, desc);
+  if(rc == BZ_OK) { rc = bz_run(ctx, BZ_JOB_REFRACT, desc); }
   if(rc != BZ_OK) { return rc; }
-  BZ_CUDA(cudaMemcpyAsync(h_out_start, os, n * 12u, cudaMemcpyDeviceToHost, 0));
-  BZ_CUDA(cudaMemcpyAsync(h_out_dir, od, n * 12u, cudaMemcpyDeviceToHost, 0));
-  BZ_CUDA(cudaMemcpyAsync(h_out_status, ost, n * 4u, cudaMemcpyDeviceToHost, 0));
-  if(h_out_patch != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_patch, op, n * 4u, cudaMemcpyDeviceToHost, 0)); }
-  BZ_CUDA(cudaStreamSynchronize(0));
+  BZ_CUDA(cudaMemcpyAsync(h_out_start, os, n * 12u, cudaMemcpyDeviceToHost, st));
+  BZ_CUDA(cudaMemcpyAsync(h_out_dir, od, n * 12u, cudaMemcpyDeviceToHost, st));
+  BZ_CUDA(cudaMemcpyAsync(h_out_status, ost, n * 4u, cudaMemcpyDeviceToHost, st));
+  if(h_out_patch != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_patch, op, n * 4u, cudaMemcpyDeviceToHost, st)); }
+  BZ_CUDA(cudaStreamSynchronize(st));
   return BZ_OK;
 }
 
@@ -688,23 +857,29 @@ int bz_intersect_batch_host(bz_lens *lens, const float *h_start, const float *h_
   if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
   if(n == 0u) { return BZ_OK; }
   if(h_start == nullptr || h_dir == nullptr || h_out_what == nullptr) { return bz_fail(BZ_ERR_INVALID, "null ray buffer"); }
-  int rc = bz_scratch(lens, (size_t)n * 76u);
+  bz_host_call call(lens);
+  if(call.rc != BZ_OK) { return call.rc; }
+  bz_context *ctx = call.ctx;
+  cudaStream_t const st = ctx->stream;
+  int rc = bz_scratch(ctx, (size_t)n * 76u);
   if(rc != BZ_OK) { return rc; }
-  float *ds = (float*)lens->d_scratch, *dd = ds + n * 3u, *opt = dd + n * 3u, *onr = opt + n * 3u, *oba = onr + n * 3u;
+  float *ds = (float*)ctx->d_scratch, *dd = ds + n * 3u, *opt = dd + n * 3u, *onr = opt + n * 3u, *oba = onr + n * 3u;
   float *odi = oba + n * 3u, *oco = odi + n;
   uint32_t *owh = (uint32_t*)(oco + n), *opa = owh + n;
-  BZ_CUDA(cudaMemcpyAsync(ds, h_start, n * 12u, cudaMemcpyHostToDevice, 0));
-  BZ_CUDA(cudaMemcpyAsync(dd, h_dir, n * 12u, cudaMemcpyHostToDevice, 0));
-  rc = bz_intersect_batch(lens, ds, dd, n, owh, opa, odi, opt, onr, oco, oba, nullptr);
+  BZ_CUDA(cudaMemcpyAsync(ds, h_start, n * 12u, cudaMemcpyHostToDevice, st));
+  BZ_CUDA(cudaMemcpyAsync(dd, h_dir, n * 12u, cudaMemcpyHostToDevice, st));
+  bz_job desc;
+  rc = bz_intersect_job(ds, dd, n, owh, opa, odi, opt, onr, oco, oba, desc);
+  if(rc == BZ_OK) { rc = bz_run(ctx, BZ_JOB_INTERSECT, desc); }
   if(rc != BZ_OK) { return rc; }
-  BZ_CUDA(cudaMemcpyAsync(h_out_what, owh, n * 4u, cudaMemcpyDeviceToHost, 0));
-  if(h_out_patch != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_patch, opa, n * 4u, cudaMemcpyDeviceToHost, 0)); }
-  if(h_out_distance != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_distance, odi, n * 4u, cudaMemcpyDeviceToHost, 0)); }
-  if(h_out_cos != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_cos, oco, n * 4u, cudaMemcpyDeviceToHost, 0)); }
-  if(h_out_point != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_point, opt, n * 12u, cudaMemcpyDeviceToHost, 0)); }
-  if(h_out_normal != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_normal, onr, n * 12u, cudaMemcpyDeviceToHost, 0)); }
-  if(h_out_bary != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_bary, oba, n * 12u, cudaMemcpyDeviceToHost, 0)); }
-  BZ_CUDA(cudaStreamSynchronize(0));
+  BZ_CUDA(cudaMemcpyAsync(h_out_what, owh, n * 4u, cudaMemcpyDeviceToHost, st));
+  if(h_out_patch != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_patch, opa, n * 4u, cudaMemcpyDeviceToHost, st)); }
+  if(h_out_distance != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_distance, odi, n * 4u, cudaMemcpyDeviceToHost, st)); }
+  if(h_out_cos != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_cos, oco, n * 4u, cudaMemcpyDeviceToHost, st)); }
+  if(h_out_point != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_point, opt, n * 12u, cudaMemcpyDeviceToHost, st)); }
+  if(h_out_normal != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_normal, onr, n * 12u, cudaMemcpyDeviceToHost, st)); }
+  if(h_out_bary != nullptr) { BZ_CUDA(cudaMemcpyAsync(h_out_bary, oba, n * 12u, cudaMemcpyDeviceToHost, st)); }
+  BZ_CUDA(cudaStreamSynchronize(st));
   return BZ_OK;
 }
 
@@ -722,7 +897,11 @@ int bz_render(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uin
               uint8_t *d_rgba, bz_stats *d_stats, void *stream) {
   if(lens == nullptr || camera == nullptr || scene == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
   if(row1 < row0 || row1 > camera->height) { return bz_fail(BZ_ERR_INVALID, "bad rows"); }
-  return bz_render_common(lens, camera, scene, row0, row1 - row0, 0u, 0u, 1u, d_rgba, d_stats, (cudaStream_t)stream);
+  bz_context *ctx = nullptr;
+  int rc = bz_context_for(lens, (cudaStream_t)stream, &ctx);
+  if(rc != BZ_OK) { return rc; }
+  std::lock_guard<std::mutex> hold(ctx->busy);
+  return bz_render_common(ctx, camera, scene, row0, row1 - row0, 0u, 0u, 1u, d_rgba, d_stats);
 }
 
 uint32_t bz_striped_rows(uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t ranks) {
@@ -737,7 +916,11 @@ int bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *sc
   if(lens == nullptr || camera == nullptr || scene == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
   if(stripe_rows == 0u || ranks == 0u || rank >= ranks) { return bz_fail(BZ_ERR_INVALID, "bad stripe layout"); }
   uint32_t const rows = bz_striped_rows(camera->height, stripe_rows, rank, ranks);
-  return bz_render_common(lens, camera, scene, 0u, rows, stripe_rows, rank, ranks, d_rgba, d_stats, (cudaStream_t)stream);
+  bz_context *ctx = nullptr;
+  int rc = bz_context_for(lens, (cudaStream_t)stream, &ctx);
+  if(rc != BZ_OK) { return rc; }
+  std::lock_guard<std::mutex> hold(ctx->busy);
+  return bz_render_common(ctx, camera, scene, 0u, rows, stripe_rows, rank, ranks, d_rgba, d_stats);
 }
 
 int bz_assemble_stripes(const uint8_t *d_bands, uint32_t band_rows, uint32_t width, uint32_t height, uint32_t stripe_rows,
@@ -758,39 +941,63 @@ int bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene
   size_t const bytes = (size_t)(row1 - row0) * camera->width * 4u;
   if(bytes == 0u) { return BZ_OK; }
   if(h_rgba == nullptr) { return bz_fail(BZ_ERR_INVALID, "h_rgba is null"); }
-  int rc = bz_scratch(lens, bytes + 128u);
+  bz_host_call call(lens);
+  if(call.rc != BZ_OK) { return call.rc; }
+  bz_context *ctx = call.ctx;
+  cudaStream_t const st = ctx->stream;
+  int rc = bz_scratch(ctx, bytes + 256u);
   if(rc != BZ_OK) { return rc; }
-  bz_stats *d_stats = (bz_stats*)lens->d_scratch;
-  uint8_t *d_rgba = (uint8_t*)lens->d_scratch + 128u;
-  BZ_CUDA(cudaMemsetAsync(d_stats, 0, sizeof(bz_stats), 0));
-  rc = bz_render(lens, camera, scene, row0, row1, d_rgba, h_stats != nullptr ? d_stats : nullptr, nullptr);
+  bz_stats *d_stats = (bz_stats*)ctx->d_scratch;
+  uint8_t *d_rgba = (uint8_t*)ctx->d_scratch + 256u;
+  BZ_CUDA(cudaMemsetAsync(d_stats, 0, sizeof(bz_stats), st));
+  rc = bz_render_common(ctx, camera, scene, row0, row1 - row0, 0u, 0u, 1u, d_rgba, h_stats != nullptr ? d_stats : nullptr);
   if(rc != BZ_OK) { return rc; }
-  BZ_CUDA(cudaMemcpyAsync(h_rgba, d_rgba, bytes, cudaMemcpyDeviceToHost, 0));
+  BZ_CUDA(cudaMemcpyAsync(h_rgba, d_rgba, bytes, cudaMemcpyDeviceToHost, st));
+  bz_stats fresh;
+  uint32_t overflow = 0u;
+  if(h_stats != nullptr) { BZ_CUDA(cudaMemcpyAsync(&fresh, d_stats, sizeof(bz_stats), cudaMemcpyDeviceToHost, st)); }
+  if(ctx->d_wave != nullptr) { BZ_CUDA(cudaMemcpyAsync(&overflow, ctx->wave.counters + 3, sizeof(overflow), cudaMemcpyDeviceToHost, st)); }
+  BZ_CUDA(cudaStreamSynchronize(st));
   if(h_stats != nullptr) {
-    bz_stats fresh;
-    BZ_CUDA(cudaMemcpyAsync(&fresh, d_stats, sizeof(bz_stats), cudaMemcpyDeviceToHost, 0));
-    BZ_CUDA(cudaStreamSynchronize(0));
     uint64_t *acc = (uint64_t*)h_stats;
     const uint64_t *add = (const uint64_t*)&fresh;
     for(size_t i = 0u; i < sizeof(bz_stats) / sizeof(uint64_t); ++i) { acc[i] += add[i]; }
   }
-  BZ_CUDA(cudaStreamSynchronize(0));
-  return bz_lens_check(lens);
+  if(overflow != 0u) {
+    BZ_CUDA(cudaMemsetAsync(ctx->wave.counters + 3, 0, sizeof(overflow), st));
+    return bz_fail(BZ_ERR_OVERFLOW, "candidate list of the wavefront pipeline overflowed: the frame is incomplete; render with bz_lens_set_pipeline(lens, BZ_PIPELINE_PERSISTENT)");
+  }
+  return BZ_OK;
+}
+
+// the context of the calling thread's most recent call, if it (still) belongs to `lens`
+static bz_context *bz_last_context(const bz_lens *lens) {
+  bz_context *ctx = gLastContext;
+  return (ctx != nullptr && ctx->lens == lens) ? ctx : nullptr;
 }
 
 int bz_last_kernel_ms(bz_lens *lens, float *out_ms) {
   if(lens == nullptr || out_ms == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
   *out_ms = 0.0f;
-  if(!lens->timed) { return BZ_OK; }
+  bz_context *ctx = bz_last_context(lens);
+  if(ctx == nullptr || !ctx->timed) { return BZ_OK; }
   BZ_CUDA(cudaSetDevice(lens->device));
-  BZ_CUDA(cudaEventSynchronize(lens->ev_end));
-  BZ_CUDA(cudaEventElapsedTime(out_ms, lens->ev_begin, lens->ev_end));
+  BZ_CUDA(cudaEventSynchronize(ctx->ev_end));
+  BZ_CUDA(cudaEventElapsedTime(out_ms, ctx->ev_begin, ctx->ev_end));
   return BZ_OK;
 }
 
 int bz_last_kernel_launches(const bz_lens *lens, uint32_t *out_count) {
   if(lens == nullptr || out_count == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
-  *out_count = lens->launches;
+  bz_context *ctx = bz_last_context(lens);
+  *out_count = (ctx != nullptr) ? ctx->launches : 0u;
+  return BZ_OK;
+}
+
+int bz_last_plan_ms(const bz_lens *lens, float *out_ms) {
+  if(lens == nullptr || out_ms == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  bz_context *ctx = bz_last_context(lens);
+  *out_ms = (ctx != nullptr) ? (float)ctx->plan_ms : 0.0f;
   return BZ_OK;
 }
 
@@ -807,7 +1014,7 @@ int bz_fp32_peak_probe(int device, float *out_tflops, float *out_ms) {
   BZ_CUDA(cudaEventCreate(&a));
   BZ_CUDA(cudaEventCreate(&b));
   int const grid = prop.multiProcessorCount * 8;
-  uint32_t const iters = 1u << 16;
+  uint32_t const iters = 1u << 15;
   float best = 1e30f;
   for(int rep = 0; rep < 4; ++rep) {
     BZ_CUDA(cudaEventRecord(a, 0));
@@ -821,7 +1028,7 @@ int bz_fp32_peak_probe(int device, float *out_tflops, float *out_ms) {
   cudaEventDestroy(a);
   cudaEventDestroy(b);
   cudaFree(sink);
-  double const flop = 2.0 * 8.0 * (double)iters * 256.0 * (double)grid;
+  double const flop = 2.0 * 16.0 * (double)iters * 256.0 * (double)grid;      // BZ_PROBE_CHAINS chains (csrc/bz_kernels.cu)
   *out_tflops = (float)(flop / ((double)best * 1e-3) * 1e-12);
   if(out_ms != nullptr) { *out_ms = best; }
   return BZ_OK;
@@ -920,12 +1127,16 @@ int bz_trace_to_target(bz_lens *lens, const float *d_start, const float *d_dir, 
   bz_job desc;
   int rc = bz_target_job(lens, d_start, d_dir, n, target, max_crossings, d_bins, d_landing, d_stats, desc);
   if(rc != BZ_OK) { return rc; }
-  return bz_run(lens, BZ_JOB_TARGET, desc, (cudaStream_t)stream);
+  bz_context *ctx = nullptr;
+  rc = bz_context_for(lens, (cudaStream_t)stream, &ctx);
+  if(rc != BZ_OK) { return rc; }
+  std::lock_guard<std::mutex> hold(ctx->busy);
+  return bz_run(ctx, BZ_JOB_TARGET, desc);
 }
 
-int bz_illuminate(bz_lens *lens, const bz_emitter *emitter, const bz_target *target, uint32_t max_crossings,
-                  uint32_t *d_bins, bz_stats *d_stats, void *stream) {
-  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+// emit -> pass -> group by hemisphere patch -> trace, on the context's stream
+static int bz_illuminate_on(bz_context *ctx, const bz_emitter *emitter, const bz_target *target, uint32_t max_crossings, uint32_t *d_bins, bz_stats *d_stats) {
+  bz_lens *lens = ctx->lens;
   uint64_t rays = 0u;
   int rc = bz_check_emitter(emitter, &rays);
   if(rc != BZ_OK) { return rc; }
@@ -934,17 +1145,17 @@ int bz_illuminate(bz_lens *lens, const bz_emitter *emitter, const bz_target *tar
   rc = bz_make_belts(emitter->belts, table);
   if(rc != BZ_OK) { return rc; }
   BZ_CUDA(cudaSetDevice(lens->device));
-  // scratch of the lens handle: emitted rays, patch keys, group offsets, grouped rays
+  // scratch of the context: emitted rays, patch keys, group offsets, grouped rays
   uint32_t const ways = 64u;              // counters per patch (csrc/bz_illum.cu)
   size_t const groups = (size_t)table.patches * ways;
   size_t const keys = ((size_t)rays * 4u + 255u) / 256u * 256u, counts = ((size_t)(groups + 1u) * 4u + 255u) / 256u * 256u;
-  if(lens->d_illum == nullptr || lens->illum_bytes < (size_t)rays * 48u + keys + counts) {
-    if(lens->d_illum != nullptr) { BZ_CUDA(cudaFree(lens->d_illum)); lens->d_illum = nullptr; lens->illum_bytes = 0u; }
-    BZ_CUDA(cudaMalloc(&lens->d_illum, (size_t)rays * 48u + keys + counts));
-    lens->illum_bytes = (size_t)rays * 48u + keys + counts;
+  if(ctx->d_illum == nullptr || ctx->illum_bytes < (size_t)rays * 48u + keys + counts) {
+    if(ctx->d_illum != nullptr) { BZ_CUDA(cudaFree(ctx->d_illum)); ctx->d_illum = nullptr; ctx->illum_bytes = 0u; }
+    BZ_CUDA(cudaMalloc(&ctx->d_illum, (size_t)rays * 48u + keys + counts));
+    ctx->illum_bytes = (size_t)rays * 48u + keys + counts;
   }
-  cudaStream_t const st = (cudaStream_t)stream;
-  float *start = (float*)lens->d_illum, *dir = start + rays * 3u, *sorted_start = dir + rays * 3u, *sorted_dir = sorted_start + rays * 3u;
+  cudaStream_t const st = ctx->stream;
+  float *start = (float*)ctx->d_illum, *dir = start + rays * 3u, *sorted_start = dir + rays * 3u, *sorted_dir = sorted_start + rays * 3u;
   uint32_t *patch = (uint32_t*)(sorted_dir + rays * 3u), *group = (uint32_t*)((char*)patch + keys);
   bz_job desc;
   rc = bz_target_job(lens, sorted_start, sorted_dir, rays, target, max_crossings, d_bins, nullptr, d_stats, desc);
@@ -955,9 +1166,19 @@ int bz_illuminate(bz_lens *lens, const bz_emitter *emitter, const bz_target *tar
   BZ_CUDA(cudaMemsetAsync(group, 0, counts, st));
   BZ_CUDA(bz_launch_group_by_patch(patch, rays, table.patches, ways, group, start, dir, sorted_start, sorted_dir, lens->sm_count, st));
   desc.ray_count_dev = group + groups;
-  rc = bz_run(lens, BZ_JOB_TARGET, desc, st);
-  lens->launches += 5u;                   // emit, pass, count, scan, scatter
+  rc = bz_run(ctx, BZ_JOB_TARGET, desc);
+  ctx->launches += 5u;                   // emit, pass, count, scan, scatter
   return rc;
+}
+
+int bz_illuminate(bz_lens *lens, const bz_emitter *emitter, const bz_target *target, uint32_t max_crossings,
+                  uint32_t *d_bins, bz_stats *d_stats, void *stream) {
+  if(lens == nullptr) { return bz_fail(BZ_ERR_INVALID, "lens is null"); }
+  bz_context *ctx = nullptr;
+  int rc = bz_context_for(lens, (cudaStream_t)stream, &ctx);
+  if(rc != BZ_OK) { return rc; }
+  std::lock_guard<std::mutex> hold(ctx->busy);
+  return bz_illuminate_on(ctx, emitter, target, max_crossings, d_bins, d_stats);
 }
 
 int bz_illuminate_host(bz_lens *lens, const bz_emitter *emitter, const bz_target *target, uint32_t max_crossings,
@@ -965,24 +1186,27 @@ int bz_illuminate_host(bz_lens *lens, const bz_emitter *emitter, const bz_target
   if(lens == nullptr || target == nullptr || h_bins == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
   size_t const bytes = (size_t)target->bins_u * target->bins_v * 4u;
   if(bytes == 0u) { return bz_fail(BZ_ERR_INVALID, "bad bin counts"); }
-  int rc = bz_scratch(lens, bytes + 128u);
+  bz_host_call call(lens);
+  if(call.rc != BZ_OK) { return call.rc; }
+  bz_context *ctx = call.ctx;
+  cudaStream_t const st = ctx->stream;
+  int rc = bz_scratch(ctx, bytes + 128u);
   if(rc != BZ_OK) { return rc; }
-  bz_stats *d_stats = (bz_stats*)lens->d_scratch;
-  uint32_t *d_bins = (uint32_t*)((uint8_t*)lens->d_scratch + 128u);
-  BZ_CUDA(cudaMemsetAsync(d_stats, 0, sizeof(bz_stats), 0));
-  BZ_CUDA(cudaMemcpyAsync(d_bins, h_bins, bytes, cudaMemcpyHostToDevice, 0));      // accumulate into the caller's counts
-  rc = bz_illuminate(lens, emitter, target, max_crossings, d_bins, h_stats != nullptr ? d_stats : nullptr, nullptr);
+  bz_stats *d_stats = (bz_stats*)ctx->d_scratch;
+  uint32_t *d_bins = (uint32_t*)((uint8_t*)ctx->d_scratch + 128u);
+  BZ_CUDA(cudaMemsetAsync(d_stats, 0, sizeof(bz_stats), st));
+  BZ_CUDA(cudaMemcpyAsync(d_bins, h_bins, bytes, cudaMemcpyHostToDevice, st));      // accumulate into the caller's counts
+  rc = bz_illuminate_on(ctx, emitter, target, max_crossings, d_bins, h_stats != nullptr ? d_stats : nullptr);
   if(rc != BZ_OK) { return rc; }
-  BZ_CUDA(cudaMemcpyAsync(h_bins, d_bins, bytes, cudaMemcpyDeviceToHost, 0));
+  BZ_CUDA(cudaMemcpyAsync(h_bins, d_bins, bytes, cudaMemcpyDeviceToHost, st));
+  bz_stats fresh;
+  if(h_stats != nullptr) { BZ_CUDA(cudaMemcpyAsync(&fresh, d_stats, sizeof(bz_stats), cudaMemcpyDeviceToHost, st)); }
+  BZ_CUDA(cudaStreamSynchronize(st));
   if(h_stats != nullptr) {
-    bz_stats fresh;
-    BZ_CUDA(cudaMemcpyAsync(&fresh, d_stats, sizeof(bz_stats), cudaMemcpyDeviceToHost, 0));
-    BZ_CUDA(cudaStreamSynchronize(0));
     uint64_t *acc = (uint64_t*)h_stats;
     const uint64_t *add = (const uint64_t*)&fresh;
     for(size_t i = 0u; i < sizeof(bz_stats) / sizeof(uint64_t); ++i) { acc[i] += add[i]; }
   }
-  BZ_CUDA(cudaStreamSynchronize(0));
   return BZ_OK;
 }
 

@@ -457,15 +457,22 @@ __global__ void bz_raygen_kernel(const bz_camera cam, uint32_t row0, uint64_t co
   }
 }
 
-// FP32 issue-rate probe: `chains` independent FMA chains per thread, `iters` dependent steps each.
-__global__ void bz_fma_probe_kernel(float *sink, uint32_t iters) {
-  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.0f, a2 = a0 + 2.0f, a3 = a0 + 3.0f, a4 = a0 + 4.0f, a5 = a0 + 5.0f, a6 = a0 + 6.0f, a7 = a0 + 7.0f;
+// FP32 issue-rate probe: BZ_PROBE_CHAINS independent FMA chains per thread (enough to cover the 4-cycle latency of the pipe
+// at any occupancy), `iters` dependent steps each, the loop unrolled so that loop control is < 2 % of the issue slots.
+#define BZ_PROBE_CHAINS 16
+__global__ void __launch_bounds__(256) bz_fma_probe_kernel(float *sink, uint32_t iters) {
+  float a[BZ_PROBE_CHAINS];
+#pragma unroll
+  for(int k = 0; k < BZ_PROBE_CHAINS; ++k) { a[k] = threadIdx.x * 1e-3f + (float)k; }
   const float m = 0.999f, c = 1e-4f;
+#pragma unroll 4
   for(uint32_t i = 0u; i < iters; ++i) {
-    a0 = __fmaf_rn(a0, m, c); a1 = __fmaf_rn(a1, m, c); a2 = __fmaf_rn(a2, m, c); a3 = __fmaf_rn(a3, m, c);
-    a4 = __fmaf_rn(a4, m, c); a5 = __fmaf_rn(a5, m, c); a6 = __fmaf_rn(a6, m, c); a7 = __fmaf_rn(a7, m, c);
+#pragma unroll
+    for(int k = 0; k < BZ_PROBE_CHAINS; ++k) { a[k] = __fmaf_rn(a[k], m, c); }
   }
-  float r = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+  float r = 0.0f;
+#pragma unroll
+  for(int k = 0; k < BZ_PROBE_CHAINS; ++k) { r += a[k]; }
   if(r == 123.456f) { sink[0] = r; }
 }
 

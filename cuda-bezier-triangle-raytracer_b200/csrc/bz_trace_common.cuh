@@ -9,8 +9,14 @@
 enum { BZC_PRIMARY = 0, BZC_CALLS, BZC_STAGE_A, BZC_STAGE_B, BZC_SNELL, BZC_ENTER, BZC_EXIT, BZC_LOST, BZC_NODES, BZC_PNODES, BZC_PWALKS, BZC_LWALKS };
 #define BZ_NSTAT     12
 
+// STAGED: the record sits in a shared-memory staging buffer, float4 i of this lane at p[i * 32] (csrc/bz_wave.cu); else in the
+// global table at p[i]
+template<bool STAGED>
+__device__ __forceinline__ float4 bzw_word4(const float4 *p, int i) { return STAGED ? p[i * 32] : __ldg(p + i); }
+
+template<bool STAGED = false>
 __device__ __forceinline__ void bzw_unpack_cull(const float4 *p, bz_cull_rec &c, uint32_t &index) {
-  float4 r0 = __ldg(p), r1 = __ldg(p + 1), r2 = __ldg(p + 2), r3 = __ldg(p + 3);
+  float4 r0 = bzw_word4<STAGED>(p, 0), r1 = bzw_word4<STAGED>(p, 1), r2 = bzw_word4<STAGED>(p, 2), r3 = bzw_word4<STAGED>(p, 3);
   c.n = bz_v(r0.x, r0.y, r0.z); c.k = r0.w;
   c.b0 = bz_v(r1.x, r1.y, r1.z); c.h_in = r1.w;
   c.b1 = bz_v(r2.x, r2.y, r2.z); c.h_out = r2.w;
@@ -45,11 +51,12 @@ __device__ __forceinline__ bzv3 bzw_normalized_rn(const bzv3 &v) {
 
 #if defined(BZ_FAST)
 // control points and dirB: words 0..32 of the stage-B record ((x, y) of the ten control points, their z, dirB)
+template<bool STAGED = false>
 __device__ __forceinline__ void bzw_load_newton_root(const float4 *p, bz_newton_rec &t) {
   float w[36];
 #pragma unroll
   for(int i = 0; i < 9; ++i) {
-    float4 r = __ldg(p + i);
+    float4 r = bzw_word4<STAGED>(p, i);
     w[4 * i] = r.x; w[4 * i + 1] = r.y; w[4 * i + 2] = r.z; w[4 * i + 3] = r.w;
   }
 #pragma unroll
@@ -64,11 +71,12 @@ struct bzw_newton2 {
   float  one;
 };
 
+template<bool STAGED = false>
 __device__ __forceinline__ void bzw_load_newton2(const float4 *p, float one, bzw_newton2 &t) {
   float w[36];
 #pragma unroll
   for(int i = 0; i < 9; ++i) {
-    float4 r = __ldg(p + i);
+    float4 r = bzw_word4<STAGED>(p, i);
     w[4 * i] = r.x; w[4 * i + 1] = r.y; w[4 * i + 2] = r.z; w[4 * i + 3] = r.w;
   }
 #pragma unroll

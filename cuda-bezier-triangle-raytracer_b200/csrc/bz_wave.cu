@@ -21,6 +21,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <math.h>
+#include <algorithm>
 #include "bz_device.h"
 #if defined(BZ_FAST)
 #define BZ_NS bz_fast_wave
@@ -87,13 +88,36 @@ __device__ __forceinline__ void bzv_flush(bzv_walk_pool &P, const bz_wave &W, ui
   else {
     for(uint32_t i = lane; i < n; i += 32u) {
       const uint32_t slot = P.qb_slot[i], index = base + i;
-      W.cand[index] = make_uint2(slot_base + slot, P.qb_patch[i]);
-      W.cand_next[index] = atomicExch(&P.head[slot], index + 1u);
+      __stcs(W.cand + index, make_uint2(slot_base + slot, P.qb_patch[i]));      // (the lists are written once and read once: streaming)
+      __stcs(W.cand_next + index, atomicExch(&P.head[slot], index + 1u));
     }
   }
   __syncwarp();
   if(lane == 0u) { P.qb_n = 0u; }
   __syncwarp();
+}
+
+// Work distribution of the walk kernel: a CTA takes whole tiles of the chunk from a global counter, its warps take the packets
+// of the tile from a shared-memory word (tile << 32 | packets handed out) -- the warps of an SM work in one image
+// neighbourhood and meet the same hierarchy nodes and patch records in L1 (as in csrc/bz_trace.cu).  The warp whose packet
+// is the first one past the end of the tile fetches the next tile and takes its first packet; the others wait for it.
+__device__ __forceinline__ unsigned long long bzv_fetch_tile(const bz_wave &W) {
+  const uint32_t next = atomicAdd(W.counters, 1u);
+  return (unsigned long long)(next < W.tile_count ? next : BZ_END) << 32;
+}
+
+__device__ __forceinline__ unsigned long long bzv_take_packet(unsigned long long *cta_work, const bz_wave &W) {
+  for(;;) {
+    const unsigned long long w = atomicAdd(cta_work, 1ull);
+    const uint32_t tile = (uint32_t)(w >> 32), at = (uint32_t)w;
+    if(tile == BZ_END || at < W.packets_per_tile) { return w; }
+    if(at == W.packets_per_tile) {
+      const unsigned long long fresh = bzv_fetch_tile(W);
+      atomicExch(cta_work, fresh | 1ull);
+      return fresh;
+    }
+    while((uint32_t)(*(volatile unsigned long long*)cta_work >> 32) == tile) { __nanosleep(64); }
+  }
 }
 
 // ------------------------------------------------------------------ walk + stage A ----
@@ -103,24 +127,26 @@ __global__ void __launch_bounds__(32 * BZV_WALK_WARPS, BZV_WALK_CTAS) bz_wave_wa
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t spp = J.camera.strata * J.camera.strata;
   const uint32_t direct_end = T.always_first + T.always_count;
-  const uint32_t packets = W.tile_count * W.packets_per_tile;
+  __shared__ unsigned long long cta_work;
   const uint32_t below = (1u << lane) - 1u;
   const float one = J.one;
   if(lane == 0u) { P.qa_n = 0u; P.qb_n = 0u; }
   if(lane < BZ_NSTAT) { P.count[lane] = 0ull; }
-  __syncwarp();
+  if(threadIdx.x == 0u) { cta_work = bzv_fetch_tile(W); }
+  __syncthreads();                           // the only CTA barrier of the kernel
 
   for(;;) {
-    uint32_t packet = 0u;
-    if(lane == 0u) { packet = atomicAdd(W.counters, 1u); }
-    packet = __shfl_sync(0xffffffffu, packet, 0);
-    if(packet >= packets) { break; }
+    unsigned long long work = 0ull;
+    if(lane == 0u) { work = bzv_take_packet(&cta_work, W); }
+    work = __shfl_sync(0xffffffffu, work, 0);
+    const uint32_t in_chunk = (uint32_t)(work >> 32), in_tile = (uint32_t)work;
+    if(in_chunk == BZ_END) { break; }
+    const uint32_t packet = in_chunk * W.packets_per_tile + in_tile;
     const uint32_t slot_base = packet * 32u, ray_slot = slot_base + lane;
     // ---- the packet's rays: generated (first crossing) or reloaded ----
     bzv3 s = bz_v(0.0f, 0.0f, 0.0f), d = s;
     bool live = false;
     if(W.level == 0u) {
-      const uint32_t in_chunk = packet / W.packets_per_tile, in_tile = packet - in_chunk * W.packets_per_tile;
       const uint32_t tile = bzv_tile_of(J, W.first_tile + in_chunk);
       const uint32_t at = in_tile * 32u + lane;
       const uint32_t inside = bzw_div(at, J.div_spp), sample = at - inside * spp;      // pixel of the tile in Morton order, sample of the pixel
@@ -133,8 +159,8 @@ __global__ void __launch_bounds__(32 * BZV_WALK_WARPS, BZV_WALK_CTAS) bz_wave_wa
         bzw_primary_ray(J.camera, J.two_over_w, J.two_over_h, px, bzw_frame_row(J, row), sample - sy * J.camera.strata, sy, s, d);
         pixel = row * J.camera.width + px;
       }
-      W.ray_a[ray_slot] = make_float4(s.x, s.y, s.z, d.x);
-      W.ray_b[ray_slot] = make_float4(d.y, d.z, __uint_as_float(pixel), __uint_as_float(live ? (1u | (BZ_STATUS_INSIDE << 1)) : 0u));
+      __stcs(W.ray_a + ray_slot, make_float4(s.x, s.y, s.z, d.x));
+      __stcs(W.ray_b + ray_slot, make_float4(d.y, d.z, __uint_as_float(pixel), __uint_as_float(live ? (1u | (BZ_STATUS_INSIDE << 1)) : 0u)));
     }
     else {
       const float4 b = W.ray_b[ray_slot];
@@ -369,7 +395,7 @@ __global__ void __launch_bounds__(32 * BZV_WALK_WARPS, BZV_WALK_CTAS) bz_wave_wa
       BZV_COUNT(BZC_NODES, steps);
       bzv_flush(P, W, slot_base, lane);
     }
-    if(live) { W.head[ray_slot] = P.head[lane]; }
+    if(live) { __stcs(W.head + ray_slot, P.head[lane]); }
     __syncwarp();
   }
   __syncwarp();
@@ -377,70 +403,125 @@ __global__ void __launch_bounds__(32 * BZV_WALK_WARPS, BZV_WALK_CTAS) bz_wave_wa
 }
 
 // ------------------------------------------------------------------ stage B ----
-struct bzv_eval_pool {                     // one per warp, shared memory: follow-side hops waiting for their evaluation
-  uint32_t hop_index[BZV_HOP_CAP];         // the candidate the hop belongs to
-  uint32_t hop_patch[BZV_HOP_CAP];         // the neighbour patch to evaluate
+#define BZV_STAGE_F4 15                    // float4 per candidate in the staging buffer: ray 2, stage-A record 4, control points + dirB 9
+
+struct bzv_eval_pool {                     // one per warp, shared memory
+  float4   stage[BZV_STAGE_F4][32];        // the inputs of the warp's NEXT batch, copied in by cp.async while the current one is evaluated
+  uint32_t hop_index[BZV_HOP_CAP];         // follow-side hops waiting for their evaluation: the candidate the hop belongs to
+  uint32_t hop_patch[BZV_HOP_CAP];         //                                                the neighbour patch to evaluate
   uint32_t hop_n;
 };
 
+__device__ __forceinline__ void bzv_copy16(float4 *to_shared, const float4 *from_global) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"((uint32_t)__cvta_generic_to_shared(to_shared)), "l"(from_global));
+}
+
+// ray, stage-A record and stage-B record (without the divider planes) of one candidate -> this lane's column of the staging buffer
+__device__ __forceinline__ void bzv_stage(bzv_eval_pool &P, const bz_tables &T, const bz_wave &W, uint2 entry, uint32_t lane) {
+  bzv_copy16(&P.stage[0][lane], W.ray_a + entry.x);
+  bzv_copy16(&P.stage[1][lane], W.ray_b + entry.x);
+  const float4 *cull = T.cull + (size_t)entry.y * BZ_CULL_F4, *newton = T.newton + (size_t)entry.y * BZ_NEWTON_F4;
+#pragma unroll
+  for(int i = 0; i < BZ_CULL_F4; ++i) { bzv_copy16(&P.stage[2 + i][lane], cull + i); }
+#pragma unroll
+  for(int i = 0; i < 9; ++i) { bzv_copy16(&P.stage[6 + i][lane], newton + i); }
+}
+
+// One candidate per lane.  Batches of 32 candidates are dealt to the warps of the grid round-robin (every batch costs the
+// same: a fixed six-trip loop).  The list is read two batches ahead and the inputs of the next batch -- its rays (a gather from
+// the ray buffer in HBM) and its patch records (L2) -- are staged into shared memory by cp.async while the current batch is
+// in its root search, so a batch starts on data that is already on the SM (north_star subsystem 1: tables staged per block
+// through shared memory).  Hops are evaluated from a small per-warp queue, 32 at a time, with direct loads.
 __global__ void __launch_bounds__(32 * BZV_EVAL_WARPS, BZV_EVAL_CTAS) bz_wave_eval_kernel(const bz_tables T, const bz_wave W, const float one, unsigned long long *stats) {
-  __shared__ bzv_eval_pool pools[BZV_EVAL_WARPS];
+  __shared__ __align__(16) bzv_eval_pool pools[BZV_EVAL_WARPS];
   bzv_eval_pool &P = pools[threadIdx.x >> 5];
   const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t total = min(__ldg(W.counters + 1), W.cand_cap);
+  const uint32_t total = (W.counters[3] != 0u) ? 0u : min(W.counters[1], W.cand_cap);      // (after an overflow the list has holes: nothing is evaluated, bz_lens_check reports it)
+  if(blockIdx.x == 0u && threadIdx.x == 0u) { W.counters[0] = 0u; }                        // the walk kernel of this pass is done: its tile counter, for the next pass
   uint32_t evaluations = 0u, hop_tests = 0u;      // per lane
-  bool exhausted = false;
+  const uint32_t stride = gridDim.x * BZV_EVAL_WARPS * 32u;
+  uint32_t first = (blockIdx.x * BZV_EVAL_WARPS + (threadIdx.x >> 5)) * 32u;               // the warp's next batch of the list
+  // entry_now: the batch at `first`, its inputs staged (or in flight); entry_next: the batch after it
+  uint2 entry_now = make_uint2(0u, 0u), entry_next = make_uint2(0u, 0u);
+  if(first + lane < total) { entry_now = __ldcs(W.cand + first + lane); }
+  if(first + stride + lane < total) { entry_next = __ldcs(W.cand + first + stride + lane); }
+  if(first + lane < total) { bzv_stage(P, T, W, entry_now, lane); }
+  asm volatile("cp.async.commit_group;");
   if(lane == 0u) { P.hop_n = 0u; }
   __syncwarp();
   for(;;) {
-    // the next batch: 32 hops when there are that many (or nothing else is left), else 32 candidates of the list
+    // the next batch: 32 hops when there are that many (or nothing else is left), else the warp's next 32 candidates of the list
     __syncwarp();
     const uint32_t hops = P.hop_n;
     __syncwarp();
     uint32_t index = 0u, patch = 0u;
-    bool active = false, first_level = true;
-    if(hops >= 32u || (exhausted && hops != 0u)) {
+    uint2 entry = make_uint2(0u, 0u), entry_ahead = make_uint2(0u, 0u);
+    bool active = false, first_level = true, reloaded = false;
+    float4 ra = make_float4(0.0f, 0.0f, 0.0f, 0.0f), rb = ra;
+    bz_cull_rec c;
+    uint32_t own;
+    bz_newton_rec t;
+#if !defined(BZ_FAST)
+    bzw_newton2 t2;
+#endif
+    if(hops >= 32u || (first >= total && hops != 0u)) {
       const uint32_t n = min(hops, 32u);
       if(lane < n) {
         index = P.hop_index[hops - n + lane];
         patch = P.hop_patch[hops - n + lane];
+        entry = __ldcs(W.cand + index);
         active = true;
+        ra = W.ray_a[entry.x];
+        rb = W.ray_b[entry.x];
+        bzw_unpack_cull(T.cull + (size_t)patch * BZ_CULL_F4, c, own);
+#if defined(BZ_FAST)
+        bzw_load_newton_root(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
+#else
+        bzw_load_newton2(T.newton + (size_t)patch * BZ_NEWTON_F4, one, t2);
+#endif
       }
       first_level = false;
       __syncwarp();
       if(lane == 0u) { P.hop_n = hops - n; }
     }
-    else if(!exhausted) {
-      uint32_t first = 0u;
-      if(lane == 0u) { first = atomicAdd(W.counters + 2, 32u); }
-      first = __shfl_sync(0xffffffffu, first, 0);
-      if(first >= total) { exhausted = true; continue; }
+    else if(first < total) {
       index = first + lane;
       active = index < total;
-      if(active) { patch = W.cand[index].y; }
+      entry = entry_now;
+      patch = entry.y;
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncwarp();
+      if(active) {
+        ra = P.stage[0][lane];
+        rb = P.stage[1][lane];
+        bzw_unpack_cull<true>(&P.stage[2][lane], c, own);
+#if defined(BZ_FAST)
+        bzw_load_newton_root<true>(&P.stage[6][lane], t);
+#else
+        bzw_load_newton2<true>(&P.stage[6][lane], one, t2);
+#endif
+      }
+      __syncwarp();
+      // the buffer is free again: the inputs of the batch after this one, and the list two batches ahead
+      first += stride;
+      entry_now = entry_next;
+      if(first + lane < total) { bzv_stage(P, T, W, entry_now, lane); }
+      asm volatile("cp.async.commit_group;");
+      if(first + stride + lane < total) { entry_ahead = __ldcs(W.cand + first + stride + lane); }
+      reloaded = true;
     }
     else { break; }
-    __syncwarp();
     if(active) {
-      const uint2 entry = W.cand[index];
-      const float4 ra = W.ray_a[entry.x], rb = W.ray_b[entry.x];
       const bzv3 s = bz_v(ra.x, ra.y, ra.z), d = bz_v(ra.w, rb.x, rb.y);
-      bz_cull_rec c;
-      uint32_t own;
-      bzw_unpack_cull(T.cull + (size_t)patch * BZ_CULL_F4, c, own);
       unsigned long long key = BZ_KEY_NONE;
       float cosine, distance;
       if(!first_level) { ++hop_tests; }
       if(bz_stage_a(c, s, d, first_level, cosine, distance)) {
         bz_hit hit;
         hit.what = BZ_MISS;
-        bz_newton_rec t;
 #if defined(BZ_FAST)
-        bzw_load_newton_root(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
         if(bz_stage_b_root(c, t, s, d, cosine, distance, hit)) {
 #else
-        bzw_newton2 t2;
-        bzw_load_newton2(T.newton + (size_t)patch * BZ_NEWTON_F4, one, t2);
         if(bz_stage_b_root(c, t2, s, d, cosine, distance, hit)) {
 #endif
           bzw_load_newton_side(T.newton + (size_t)patch * BZ_NEWTON_F4, t);
@@ -456,12 +537,16 @@ __global__ void __launch_bounds__(32 * BZV_EVAL_WARPS, BZV_EVAL_CTAS) bz_wave_ev
         }
         else if(hit.what == BZ_HIT && hit.distance < 3.402823466e+38f) {      // bezierMesh.cpp:209, 220
           key = bzw_make_key(hit.distance, entry.y);                           // loop index = the patch the loop stood at
-          W.cand_pay[2u * (size_t)index] = make_float4(hit.point.x, hit.point.y, hit.point.z, hit.cos_incidence);
-          W.cand_pay[2u * (size_t)index + 1u] = make_float4(hit.normal.x, hit.normal.y, hit.normal.z, __uint_as_float(patch));
+          __stcs(W.cand_pay + 2u * (size_t)index, make_float4(hit.point.x, hit.point.y, hit.point.z, hit.cos_incidence));
+          __stcs(W.cand_pay + 2u * (size_t)index + 1u, make_float4(hit.normal.x, hit.normal.y, hit.normal.z, __uint_as_float(patch)));
         }
       }
-      if(first_level || key != BZ_KEY_NONE) { W.cand_key[index] = key; }
+      if(first_level || key != BZ_KEY_NONE) { __stcs(W.cand_key + index, key); }
     }
+    // the list entries requested before the root search are taken over only now: touching the destination of a load in
+    // flight (even to copy it into the loop-carried register) would park the warp on it for a whole DRAM round trip
+    asm volatile("" : "+r"(entry_ahead.x), "+r"(entry_ahead.y));
+    if(reloaded) { entry_next = entry_ahead; }
   }
   evaluations = __reduce_add_sync(0xffffffffu, evaluations);
   hop_tests = __reduce_add_sync(0xffffffffu, hop_tests);
@@ -475,26 +560,32 @@ __global__ void __launch_bounds__(32 * BZV_EVAL_WARPS, BZV_EVAL_CTAS) bz_wave_ev
 __global__ void __launch_bounds__(256) bz_wave_resolve_kernel(const bz_tables T, const bz_job J, const bz_wave W) {
   const uint32_t rays = W.tile_count * W.packets_per_tile * 32u;
   const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if(slot == 0u) { W.counters[1] = 0u; }      // the evaluation of this pass is done: the candidate count, for the next pass
+  const bool last = (W.level + 1u >= max(1u, J.scene.max_crossings));      // every ray ends here: nothing is kept
   uint32_t events = 0u;                    // byte 0 Snell block reached, 1 entered, 2 exited, 3 lost
   if(slot < rays) {
-    const float4 rb = W.ray_b[slot];
+    // the three loads of a ray are issued together (the kernel is latency-bound: one dependent step less per ray)
+    const float4 rb = __ldcs(W.ray_b + slot);
+    const float4 ra = __ldcs(W.ray_a + slot);
+    uint32_t link = __ldcs(W.head + slot);
     const uint32_t st = __float_as_uint(rb.w);
     if((st & 1u) != 0u) {
       uint32_t expected = (st >> 1) & 3u, crossings = st >> 4;
       // the nearest result of the ray's chain: (distance, loop index) keys are distinct, strict < of bezierMesh.cpp:220
       unsigned long long best = BZ_KEY_NONE;
       uint32_t winner = 0u;
-      for(uint32_t link = W.head[slot]; link != 0u; link = W.cand_next[link - 1u]) {
-        const unsigned long long key = W.cand_key[link - 1u];
+      while(link != 0u) {
+        const unsigned long long key = __ldcs(W.cand_key + (link - 1u));
+        const uint32_t next = __ldcs(W.cand_next + (link - 1u));
         if(key < best) { best = key; winner = link - 1u; }
+        link = next;
       }
-      const float4 ra = W.ray_a[slot];
       bzv3 s = bz_v(ra.x, ra.y, ra.z), d = bz_v(ra.w, rb.x, rb.y);
       const bool found = (best != BZ_KEY_NONE);
       uint32_t status = BZ_STATUS_NONE;
       bzv3 refracted = d, point = s;
       if(found) {
-        const float4 p0 = W.cand_pay[2u * (size_t)winner], p1 = W.cand_pay[2u * (size_t)winner + 1u];
+        const float4 p0 = __ldcs(W.cand_pay + 2u * (size_t)winner), p1 = __ldcs(W.cand_pay + 2u * (size_t)winner + 1u);
         point = bz_v(p0.x, p0.y, p0.z);
         status = bz_snell(T.ri, p0.w, bz_v(p1.x, p1.y, p1.z), refracted);
         events |= 1u;
@@ -516,7 +607,7 @@ __global__ void __launch_bounds__(256) bz_wave_resolve_kernel(const bz_tables T,
         if(expected == BZ_STATUS_INSIDE) { value = bzw_shade_background(J.scene, s, d); }      // the ray is in air: it reaches the background
         else { value = J.scene.value_lost; events |= 0x1000000u; }                             // entered and never left
         atomicAdd(J.accum + __float_as_uint(rb.z), value);
-        W.ray_b[slot] = make_float4(rb.x, rb.y, rb.z, __uint_as_float(0u));
+        if(!last) { W.ray_b[slot] = make_float4(rb.x, rb.y, rb.z, __uint_as_float(0u)); }
       }
       else {
         W.ray_a[slot] = make_float4(s.x, s.y, s.z, d.x);
@@ -541,29 +632,30 @@ using namespace BZ_NS;
 
 static size_t bzv_walk_shared() { return sizeof(bzv_walk_pool) * BZV_WALK_WARPS; }
 
-// One crossing of one chunk: walk + stage A, stage B, resolve, stream-ordered.  `counters` [0..2] are zeroed first.
+// One crossing of one chunk: walk + stage A, stage B, resolve, stream-ordered.  `counters` [0..2] are zero on entry (the handle
+// zeroes them once per frame) and are left zero: each kernel resets what the kernel before it consumed.
 cudaError_t BZ_SYM(bz_launch_wave_pass)(const bz_tables &tables, const bz_job &desc, const bz_wave &wave, int sm_count, cudaStream_t stream) {
-  static bool configured[64] = {};
+  static int walk_ctas[64] = {}, eval_ctas[64] = {};          // resident CTAs per SM, per device (0: not asked yet)
   int device = 0;
   cudaError_t e = cudaGetDevice(&device);
   if(e != cudaSuccess) { return e; }
-  if(!configured[device & 63]) {
+  device &= 63;
+  if(walk_ctas[device] == 0) {
     e = cudaFuncSetAttribute(bz_wave_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bzv_walk_shared());
     if(e != cudaSuccess) { return e; }
-    configured[device & 63] = true;
+    int walk = 0, eval = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&walk, bz_wave_walk_kernel, 32 * BZV_WALK_WARPS, bzv_walk_shared());
+    if(e != cudaSuccess) { return e; }
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&eval, bz_wave_eval_kernel, 32 * BZV_EVAL_WARPS, 0);
+    if(e != cudaSuccess) { return e; }
+    eval_ctas[device] = eval > 0 ? eval : 1;
+    walk_ctas[device] = walk > 0 ? walk : 1;
   }
   const uint32_t packets = wave.tile_count * wave.packets_per_tile;
   if(packets == 0u) { return cudaSuccess; }
-  e = cudaMemsetAsync(wave.counters, 0, 3u * sizeof(uint32_t), stream);
-  if(e != cudaSuccess) { return e; }
-  int walk_ctas = 0, eval_ctas = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&walk_ctas, bz_wave_walk_kernel, 32 * BZV_WALK_WARPS, bzv_walk_shared());
-  if(e != cudaSuccess) { return e; }
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&eval_ctas, bz_wave_eval_kernel, 32 * BZV_EVAL_WARPS, 0);
-  if(e != cudaSuccess) { return e; }
-  const uint32_t walk_grid = (uint32_t)sm_count * (uint32_t)(walk_ctas > 0 ? walk_ctas : 1);
-  bz_wave_walk_kernel<<<(packets + BZV_WALK_WARPS - 1u) / BZV_WALK_WARPS < walk_grid ? (packets + BZV_WALK_WARPS - 1u) / BZV_WALK_WARPS : walk_grid, 32 * BZV_WALK_WARPS, bzv_walk_shared(), stream>>>(tables, desc, wave);
-  bz_wave_eval_kernel<<<(uint32_t)sm_count * (uint32_t)(eval_ctas > 0 ? eval_ctas : 1), 32 * BZV_EVAL_WARPS, 0, stream>>>(tables, wave, desc.one, desc.stats);
+  const uint32_t walk_grid = std::min<uint32_t>((packets + BZV_WALK_WARPS - 1u) / BZV_WALK_WARPS, (uint32_t)sm_count * (uint32_t)walk_ctas[device]);
+  bz_wave_walk_kernel<<<walk_grid, 32 * BZV_WALK_WARPS, bzv_walk_shared(), stream>>>(tables, desc, wave);
+  bz_wave_eval_kernel<<<(uint32_t)sm_count * (uint32_t)eval_ctas[device], 32 * BZV_EVAL_WARPS, 0, stream>>>(tables, wave, desc.one, desc.stats);
   bz_wave_resolve_kernel<<<(packets * 32u + 255u) / 256u, 256, 0, stream>>>(tables, desc, wave);
   return cudaGetLastError();
 }

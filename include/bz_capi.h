@@ -174,9 +174,21 @@ int  bz_lens_patch_count(const bz_lens *lens, uint32_t *out_count);
 #define BZ_PIPELINE_PERSISTENT  1u
 #define BZ_PIPELINE_WAVEFRONT   2u
 int  bz_lens_set_pipeline(bz_lens *lens, uint32_t pipeline);
+/* Ray slots per chunk of the wavefront pipeline (device memory: 36 bytes per slot + 4 x 52 bytes of candidate list per slot). */
+int  bz_lens_set_wave_chunk(bz_lens *lens, uint32_t ray_slots);
 /* Synchronises with the work in flight on the handle and reports (once) a device-side overflow of the wavefront pipeline's
  * candidate list as BZ_ERR_OVERFLOW; the *_host render calls do this themselves. */
 int  bz_lens_check(bz_lens *lens);
+/* Threads and streams.  The tables of a lens are read-only after bz_lens_create; everything a call writes besides the caller's
+ * buffers (pixel accumulator, work counters, tile plan, wavefront lists, staging, timing events) lives in a CONTEXT the lens keeps per
+ * stream, made on the first call that names the stream.  So, like BezierLens::refract (const and re-entrant, reference/bezierLens.h:27):
+ *   - calls on DIFFERENT streams of one lens may overlap, from one host thread or several;
+ *   - calls on the same stream are ordered by the stream (two threads enqueueing on one stream take turns);
+ *   - the *_host calls each borrow a private context with a non-blocking stream of its own, so any number of threads may call them
+ *     side by side;
+ *   - bz_lens_set_mode / bz_lens_set_pipeline / bz_lens_set_wave_chunk change the lens for all later calls: do not race them with calls.
+ * bz_lens_release_stream waits for the stream's work and frees its context (call it before destroying a stream the lens has seen). */
+int  bz_lens_release_stream(bz_lens *lens, void *stream);
 
 /* BezierLens::refract over a batch  -- reference/bezierLens.h:27, bezierLens.cpp:4-34.
  * start/dir: n x 3 floats (dir must be unit length, as Ray::Ray leaves it, 3dGeomUtil.h:176-178).
@@ -205,8 +217,7 @@ int  bz_generate_rays(const bz_camera *camera, uint32_t row0, uint32_t row1, flo
  * R=G=B=value, A=255).  d_stats (nullable) is ACCUMULATED into (device memory, caller zeroes).
  * In BZ_MODE_CULLED the call plans the frame: tiles of pixels onto which no box of the cull hierarchy projects
  * are shaded by a separate kernel (their rays count in primary_rays and refract_calls, they do no walk), the
- * other tiles are traced.  The plan of the last frame is kept in the lens handle, so the calls on one handle
- * must not overlap in time (they share the handle's accumulator and work counter anyway). */
+ * other tiles are traced.  The plan of the last frame is kept in the stream's context (see "Threads and streams"). */
 int  bz_render(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
                uint8_t *d_rgba, bz_stats *d_stats, void *stream);
 int  bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
@@ -287,9 +298,13 @@ int  bz_lens_info(const bz_lens *lens, uint32_t out[4]);
  * TFLOP/s: the denominator of the FP32 roofline fraction. */
 int  bz_fp32_peak_probe(int device, float *out_tflops, float *out_ms);
 
-/* Device time (ms) of the intersect/refract kernels of the most recent bz_render / bz_refract_batch
- * on this lens, measured with CUDA events on the stream the call used; synchronises that stream. */
+/* Device time (ms) of the intersect/refract kernels of the calling thread's most recent bz_render* / bz_*_batch call on this lens,
+ * measured with CUDA events on the stream the call used; waits for that call's kernels. */
 int  bz_last_kernel_ms(bz_lens *lens, float *out_ms);
+
+/* Host time (ms) the most recent bz_render* call of the calling thread spent planning the frame (bz_plan_tiles: projecting the outline
+ * boxes of the cull hierarchy, classifying and ordering the tiles) and staging the tile list for upload; 0 when the kept plan of the last frame was reused. */
+int  bz_last_plan_ms(const bz_lens *lens, float *out_ms);
 
 /* Kernels the most recent bz_render* / bz_refract_batch / bz_intersect_batch / bz_trace_to_target call on this lens launched
  * (RENDER: bz_sky_kernel when the frame has tiles beside the lens, the trace kernel when it has tiles on it, the resolve). */

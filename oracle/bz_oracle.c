@@ -35,6 +35,7 @@ typedef struct bzo_hit {
   float    normal[3];
   float    bary[3];
   float    cos_incidence;
+  float    runner_up;      /* mesh_intersect: distance of the nearest accepted hit that did not win (FLT_MAX without one) */
 } bzo_hit;
 
 static const float cPlaneEpsilon      = 0.00001f;    /* Plane::csRayPlaneIntersectionEpsilon, 3dGeomUtil.h:219 */
@@ -202,6 +203,7 @@ static void mesh_intersect(const bz_patch *patches, uint32_t count, const float 
   result->what = BZO_NONE;
   result->patch = BZ_NO_PATCH;
   result->distance = 3.402823466e+38f;
+  float runner_up = 3.402823466e+38f;      /* not part of the reference: lets the tests COUNT edge-ambiguous rays (SURVEY.md section 4 iii) */
   for(uint32_t i = 0u; i < count; ++i) {
     bzo_hit candidate;
     uint32_t evaluated = i;
@@ -211,10 +213,13 @@ static void mesh_intersect(const bz_patch *patches, uint32_t count, const float 
       patch_intersect(patches + evaluated, start, dir, BZO_LIMIT_NONE, &candidate, work + 2);
     }
     if(candidate.what == BZO_INTERSECT && candidate.distance < result->distance) {
+      if(result->distance < runner_up) { runner_up = result->distance; }
       *result = candidate;
       result->patch = evaluated;
     }
+    else if(candidate.what == BZO_INTERSECT && candidate.distance < runner_up) { runner_up = candidate.distance; }
   }
+  result->runner_up = runner_up;
   work[0] += count;
 }
 
@@ -258,7 +263,7 @@ typedef struct bzo_job {
   const bz_patch *patches; uint32_t count; float ri;
   const float *start; const float *dir; const uint32_t *expected; uint64_t n;
   float *out_start; float *out_dir; uint32_t *out_status; uint32_t *out_patch;
-  uint32_t *out_what; float *out_distance; float *out_point; float *out_normal; float *out_cos; float *out_bary;
+  uint32_t *out_what; float *out_distance; float *out_point; float *out_normal; float *out_cos; float *out_bary; float *out_runner_up;
   int refract; int thread; int threads; uint64_t work[3];
 } bzo_job;
 
@@ -280,6 +285,7 @@ static void *bzo_worker(void *arg) {
       if(job->out_patch) { job->out_patch[i] = ok ? hit.patch : BZ_NO_PATCH; }
       if(job->out_distance) { job->out_distance[i] = ok ? hit.distance : 0.0f; }
       if(job->out_cos) { job->out_cos[i] = ok ? hit.cos_incidence : 0.0f; }
+      if(job->out_runner_up) { job->out_runner_up[i] = hit.runner_up; }
       for(int k = 0; k < 3; ++k) {
         if(job->out_point) { job->out_point[i * 3u + k] = ok ? hit.point[k] : 0.0f; }
         if(job->out_normal) { job->out_normal[i * 3u + k] = ok ? hit.normal[k] : 0.0f; }
@@ -327,6 +333,17 @@ void bzo_intersect_batch(const bz_patch *patches, uint32_t count, const float *s
   job.out_what = out_what; job.out_patch = out_patch; job.out_distance = out_distance; job.out_point = out_point;
   job.out_normal = out_normal; job.out_cos = out_cos; job.out_bary = out_bary; job.refract = 0;
   bzo_run(&job, threads, work);
+}
+
+/* bzo_intersect_batch plus, per ray, the distance of the nearest accepted hit that lost (FLT_MAX without one): a ray whose two
+ * best hits lie within 1e-3 of the shape size of each other sits on a patch edge (SURVEY.md section 4 iii) */
+void bzo_intersect_batch_runner_up(const bz_patch *patches, uint32_t count, const float *start, const float *dir, uint64_t n,
+                                   uint32_t *out_what, uint32_t *out_patch, float *out_distance, float *out_runner_up, int threads) {
+  bzo_job job;
+  memset(&job, 0, sizeof(job));
+  job.patches = patches; job.count = count; job.start = start; job.dir = dir; job.n = n;
+  job.out_what = out_what; job.out_patch = out_patch; job.out_distance = out_distance; job.out_runner_up = out_runner_up; job.refract = 0;
+  bzo_run(&job, threads, 0);
 }
 
 /* one patch, one ray: returns What (0..4) */

@@ -32,6 +32,8 @@ def load():
     lib.bzo_refract_batch.argtypes = [vp, u32, f, fp, fp, up, u64, fp, fp, up, up, C.c_int, wp]
     lib.bzo_intersect_batch.restype = None
     lib.bzo_intersect_batch.argtypes = [vp, u32, fp, fp, u64, up, up, fp, fp, fp, fp, fp, C.c_int, wp]
+    lib.bzo_intersect_batch_runner_up.restype = None
+    lib.bzo_intersect_batch_runner_up.argtypes = [vp, u32, fp, fp, u64, up, up, fp, fp, C.c_int]
     lib.bzo_patch_intersect.restype = u32
     lib.bzo_patch_intersect.argtypes = [vp, fp, fp, u32, fp, fp, fp, fp, fp]
     lib.bzo_interpolate.restype = None
@@ -92,6 +94,19 @@ def intersect(patches, start, direction, threads=1):
     lib.bzo_intersect_batch(patches.ctypes.data, patches.shape[0], _fp(s), _fp(d), n, _up(what), _up(patch), _fp(dist),
                             _fp(point), _fp(normal), _fp(cos), _fp(bary), threads, work.ctypes.data_as(C.POINTER(C.c_uint64)))
     return dict(what=what, patch=patch, distance=dist, point=point, normal=normal, cos=cos, bary=bary, work=work)
+
+
+def edge_ambiguous(patches, start, direction, size, threads=1):
+    """rays whose two best accepted hits lie within 1e-3 * size of each other (patch-edge duplicates, SURVEY.md section 4 iii)
+    -> boolean mask; the bit-exact tests compare these rays like all others and REPORT how many there were"""
+    lib = load()
+    patches = _table(patches)
+    s, d = _f32(start, (-1, 3)), _f32(direction, (-1, 3))
+    n = s.shape[0]
+    what, patch = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+    dist, runner = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    lib.bzo_intersect_batch_runner_up(patches.ctypes.data, patches.shape[0], _fp(s), _fp(d), n, _up(what), _up(patch), _fp(dist), _fp(runner), threads)
+    return (what == 4) & (runner < 3e38) & (np.abs(runner.astype(np.float64) - dist) < 1e-3 * size)
 
 
 def patch_intersect(patches, index, start, direction, limit):
