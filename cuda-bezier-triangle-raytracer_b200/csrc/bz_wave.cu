@@ -194,9 +194,9 @@ __global__ void __launch_bounds__(32 * BZV_WALK_WARPS, BZV_WALK_CTAS) bz_wave_wa
       const uint32_t direct_n = direct_end - direct_first;
       uint32_t sp = 1u;
       found = (direct_n + 6u) / 7u;
-      packet_done = (found <= BZV_CAND_CAP / 2u);
+      packet_done = (found <= 32u);      // one seed entry per lane; more records than that outside the hierarchy: per-lane walk
       if(packet_done) {
-        for(uint32_t e = lane; e < found; e += 32u) { P.cand[e] = ((direct_first + 7u * e) << 3) | min(7u, direct_n - 7u * e); }
+        if(lane < found) { P.cand[lane] = ((direct_first + 7u * lane) << 3) | min(7u, direct_n - 7u * lane); }
         if(lane == 0u) { P.stack[0] = 0u; }
         __syncwarp();
       }

@@ -168,7 +168,8 @@ int  bz_lens_patch_count(const bz_lens *lens, uint32_t *out_count);
 /* How bz_render* runs the tiles that can meet the lens (BZ_MODE_CULLED / BZ_MODE_FAST; the results are the same bits):
  *   BZ_PIPELINE_PERSISTENT  one persistent warp-scheduled kernel does walk, stage A, stage B and resolve (csrc/bz_trace.cu)
  *   BZ_PIPELINE_WAVEFRONT   three kernels per surface crossing over global ray / candidate lists (csrc/bz_wave.cu)
- *   BZ_PIPELINE_AUTO        wavefront for frames with at least 2^20 rays on lens tiles, else persistent (the default)
+ *   BZ_PIPELINE_AUTO        the default: the persistent kernel (on the 4K headline frame the two are level; the wavefront pipeline
+ *                           needs 36 bytes per ray slot + 208 bytes of candidate list per ray slot of device memory)
  * The batch entry points (bz_refract_batch, bz_intersect_batch, bz_trace_to_target) always use the persistent kernel. */
 #define BZ_PIPELINE_AUTO        0u
 #define BZ_PIPELINE_PERSISTENT  1u
