@@ -6,11 +6,16 @@
 
 One step = one whole frame of the workload (default: cfg4, makeEllipsoid(181,91,(1,4,2)) -> 98 826 patches,
 3840x2160, 16 rays/pixel = 132 710 400 primary rays), image rows dealt to the N ranks in round-robin stripes
-of 8 rows, tables replicated, one NCCL all-gather of the rendered stripes per step when N > 1 (strong
-scaling: the frame is fixed).  `value` = primary rays of the frame / device time per step, max over ranks.
-`e2e` goes through the host-buffer C-ABI call (bz_render_host, N = 1) or render + gather + device->pinned-host
-copy of the frame (N > 1), every step.  `--impl reference` times the reference's own CPU code
-(oracle/_ref/libbzref.so: reference sources + the one documented hoist) on the host cores.
+of 8 rows, tables replicated, the rendered stripes gathered on rank 0 by bz_gather_rows (C ABI: NCCL send / recv
+over NVLink, assembly on the device) when N > 1 (strong scaling: the frame is fixed).
+`value` = primary rays of the frame / device time per step (CUDA events around every step, the L2 flush between
+steps outside them), max over ranks.  `e2e` goes through the host-buffer C-ABI call (bz_render_host, N = 1) or
+render + gather + device->pinned-host copy of the frame (N > 1, the way home of frame k overlapping the tracing of
+frame k + 1), every step; `e2e_moving_camera` is the same with a camera that moves every step (the frame plan is
+rebuilt on the host each time); `frame_crc32` is the CRC-32 of the frame the e2e loop left in host memory -- it must
+be the same at every N.  `fast` times BZ_MODE_FAST beside the parity build and counts the pixels that differ.
+`--impl reference` times the reference's own CPU code (oracle/_ref/libbzref.so: reference sources + the one
+documented hoist) on the host cores.
 Prints ONE JSON line.
 """
 import argparse
@@ -105,7 +110,8 @@ def reference_sample(name, seconds, threads):
     if not bzref.available():
         return None
     spec, mesh, cam_kw, scene_kw = workloads.setup(name, bzref.RefMesh)
-    lens = bzref.RefLens(spec["ri"], bzref.RefBezierMesh(mesh))
+    bezier = bzref.RefBezierMesh(mesh)
+    lens = bzref.RefLens(spec["ri"], bezier)
     cam, scene = bzref.make_camera(spec["width"], spec["height"], **cam_kw), bzref.make_scene(**scene_kw)
 
     def run(step):
@@ -118,7 +124,7 @@ def reference_sample(name, seconds, threads):
     while dt < 0.6 * seconds and step > 1:
         step = max(1, min(step - 1, int(step * (max(dt, 1e-3) / seconds) ** 0.5)))
         dt, rays, stats = run(step)
-    return dict(value=rays / dt / 1e6, rays=int(rays), seconds=dt, step=step, calls=int(stats.refract_calls),
+    return dict(value=rays / dt / 1e6, rays=int(rays), seconds=dt, step=step, calls=int(stats.refract_calls), patches=int(bezier.size()),
                 sample="every %d-th pixel in x and y, all %d samples of each: %d primary rays, %d refract() calls, %.1f s on %d threads"
                        % (step, spec["strata"] ** 2, rays, stats.refract_calls, dt, threads))
 
@@ -145,7 +151,7 @@ def main_reference(args, name):
     line = {
         "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": seconds / len(timed) * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": name, "patches": None, "image": "%dx%d" % (spec["width"], spec["height"]), "spp": spec["strata"] ** 2,
+        "config": {"workload": name, "patches": timed[-1]["patches"], "image": "%dx%d" % (spec["width"], spec["height"]), "spp": spec["strata"] ** 2,
                    "note": "each step is a bounded pixel-lattice sample of the frame, rate = sampled primary rays / wall time"},
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "reference", "sample": timed[-1]["sample"], "cpu": cpu_model()},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -155,6 +161,7 @@ def main_reference(args, name):
 
 
 def main_ours(args, name):
+    import zlib
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -169,15 +176,18 @@ def main_ours(args, name):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL may print its version banner on stdout when the communicator is created: keep stdout for the ONE JSON line
+        # NCCL may print its version banner on stdout when a communicator is created: keep stdout for the ONE JSON line
         sys.stdout.flush()
         saved_stdout = os.dup(1)
         os.dup2(2, 1)
-        try:
-            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    try:
+        if world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))      # bootstrap + the scalar reductions of this script only
             dist.barrier()
-            torch.cuda.synchronize()
-        finally:
+        comm = sharding.make_comm(bz, local) if world > 1 else None                     # the image gather itself: bz_gather_rows (C ABI, NCCL send / recv to rank 0)
+        torch.cuda.synchronize()
+    finally:
+        if world > 1:
             sys.stdout.flush()
             os.dup2(saved_stdout, 1)
             os.close(saved_stdout)
@@ -188,8 +198,8 @@ def main_ours(args, name):
     spec, mesh, cam_kw, scene_kw = workloads.setup(name, bz.Mesh)
     bezier = bz.BezierMesh(mesh)
     lens = bz.BezierLens(spec["ri"], bezier, device=local)
-    if args.mode == "fast":
-        lens.set_mode(bz.MODE_FAST)
+    exact_mode, fast_mode = bz.MODE_CULLED, bz.MODE_FAST
+    lens.set_mode(fast_mode if args.mode == "fast" else exact_mode)
     lens.set_pipeline({"auto": bz.PIPELINE_AUTO, "persistent": bz.PIPELINE_PERSISTENT, "wavefront": bz.PIPELINE_WAVEFRONT}[args.pipeline])
     setup_s = time.perf_counter() - t_setup
     cam, scene = bz.make_camera(spec["width"], spec["height"], **cam_kw), bz.make_scene(**scene_kw)
@@ -200,48 +210,58 @@ def main_ours(args, name):
     frame_rays = width * height * spp
 
     dev = torch.device("cuda", local)
-    band = torch.zeros((band_rows, width, 4), dtype=torch.uint8, device=dev)          # this rank's stripes (padded to the largest band)
-    bands = torch.zeros((world, band_rows, width, 4), dtype=torch.uint8, device=dev) if world > 1 else None
-    image = torch.zeros((height, width, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else None
+    bands = [torch.zeros((band_rows, width, 4), dtype=torch.uint8, device=dev) for _ in range(2)]       # this rank's stripes, double-buffered for the pipelined e2e loop
+    images = [torch.zeros((height, width, 4), dtype=torch.uint8, device=dev) for _ in range(2)] if (world > 1 and rank == 0) else [None, None]
     stats = torch.zeros(len(bz.STAT_NAMES), dtype=torch.int64, device=dev)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)               # > 126 MB L2
-    host_image = torch.empty((height, width, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+    hosts = [torch.empty((height, width, 4), dtype=torch.uint8).pin_memory() for _ in range(2)] if rank == 0 else [None, None]
     kernel_ms = []
 
-    def step(record):
-        flush.fill_(1)                                                                  # L2 flush between iterations
-        lens.render_striped_device(cam, scene, stripe, rank, world, band, stats=stats)
-        if world > 1:
-            sharding.gather_bands(band, bands)                                          # NCCL all-gather over NVLink
-            if rank == 0:
-                bz.assemble_stripes_device(bands, band_rows, width, height, stripe, world, image)
+    def render_and_gather(buf, record):
+        lens.render_striped_device(cam, scene, stripe, rank, world, bands[buf], stats=stats)
         if record:
-            kernel_ms.append(lens.last_kernel_ms())                                     # events on the launching stream
+            kernel_ms.append(lens.last_kernel_ms())                                     # events on the launching stream around the trace kernels
+        if world > 1:
+            comm.gather_rows(bands[buf], width, height, stripe, rgba=images[buf])        # NCCL send / recv over NVLink + assembly on rank 0
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed_steps(steps, record):
+        """K steps between two barriers; every step is bracketed by its own event pair AFTER the L2 flush, so that the flush
+        (256 MiB fill, stated as flush_ms) is between the timed iterations and not inside them -> (ms per step, wall0, wall1)"""
+        pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        wall0 = time.time()
+        for begin, end in pairs:
+            flush.fill_(1)
+            begin.record()
+            render_and_gather(0, record)
+            end.record()
+        barrier()
+        wall1 = time.time()
+        total = torch.tensor([sum(b.elapsed_time(e) for b, e in pairs)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(total, op=dist.ReduceOp.MAX)
+        return float(total.item()) / steps, wall0, wall1
+
     for _ in range(args.warmup):
-        step(False)
+        flush.fill_(1)
+        render_and_gather(0, False)
     barrier()
     stats.zero_()
     sampler = ClockSampler(local) if rank == 0 else None
-    begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    wall0 = time.time()
-    begin.record()
-    for _ in range(args.steps):
-        step(True)
-    end.record()
-    barrier()
-    wall1 = time.time()
-    elapsed = torch.tensor([begin.elapsed_time(end)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)
-    ms_per_step = float(elapsed.item()) / args.steps
+    ms_per_step, wall0, wall1 = timed_steps(args.steps, True)
     clocks = sampler.stop(wall0, wall1) if sampler else None
+    fb, fe = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    fb.record()
+    for _ in range(4):
+        flush.fill_(1)
+    fe.record()
+    torch.cuda.synchronize()
+    flush_ms = fb.elapsed_time(fe) / 4
 
     # ---- work counters of the timed region, summed over ranks ----
     work = stats.clone()
@@ -251,31 +271,86 @@ def main_ours(args, name):
         dist.all_reduce(kern, op=dist.ReduceOp.MAX)
     work = dict(zip(bz.STAT_NAMES, [int(x) // args.steps for x in work.tolist()]))      # per step (frame)
     own = dict(zip(bz.STAT_NAMES, [int(x) // args.steps for x in stats.tolist()]))      # this rank, per launch
+    launches_per_step = lens.last_kernel_launches() + (1 if (world > 1 and rank == 0) else 0)       # (sky +) trace + resolve (+ the stripe assembly on rank 0)
 
     # ---- e2e: host buffers in the timed region, every step ----
-    e2e_steps = max(2, min(args.steps, 5))
+    e2e_steps = max(2, min(args.steps, 8))
+    side = torch.cuda.Stream(device=dev)
+    moving = {"plan_ms": []}
 
-    def e2e_step():
-        if world == 1:
-            lens.render_host_into(cam, scene, host_image.data_ptr())                   # C ABI: bz_render_host, D2H inside
-        else:
-            step(False)
-            if rank == 0:
-                host_image.copy_(image, non_blocking=True)
-            barrier()
+    def e2e_loop(steps, move_camera):
+        """N = 1: bz_render_host (C ABI) into pinned host memory, every step.  N > 1: render on the compute stream; gather to rank 0
+        + assembly + device->pinned-host copy on a side stream, double-buffered, so frame k's way home overlaps frame k + 1's
+        tracing; every frame is in host memory before the clock stops.  move_camera: the eye moves by one ulp per step, so every
+        step plans its frame anew (bz_plan_tiles + upload, bz_last_plan_ms)."""
+        rendered = [torch.cuda.Event() for _ in range(2)]
+        home = [torch.cuda.Event() for _ in range(2)]
+        eye0 = float(cam.eye[0])
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(steps):
+            buf = k % 2
+            if move_camera:
+                cam.eye[0] = float(np.nextafter(np.float32(cam.eye[0]), np.float32(1e30)))
+            if world == 1:
+                lens.render_host_into(cam, scene, hosts[buf].data_ptr())
+            else:
+                if k >= 2:
+                    torch.cuda.current_stream().wait_event(home[buf])                  # the band buffer is free again
+                lens.render_striped_device(cam, scene, stripe, rank, world, bands[buf])
+                rendered[buf].record()
+                with torch.cuda.stream(side):
+                    side.wait_event(rendered[buf])
+                    comm.gather_rows(bands[buf], width, height, stripe, rgba=images[buf], stream=side.cuda_stream)
+                    if rank == 0:
+                        hosts[buf].copy_(images[buf], non_blocking=True)
+                    home[buf].record()
+            if move_camera:
+                moving["plan_ms"].append(lens.last_plan_ms())
+        barrier()
+        seconds = (time.perf_counter() - t0) / steps
+        cam.eye[0] = eye0
+        t = torch.tensor([seconds], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), (steps - 1) % 2
 
-    for _ in range(max(1, min(args.warmup, 3))):                                       # the call's device scratch is allocated on first use
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    barrier()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
-    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_s = float(e2e_t.item())
+    e2e_loop(max(2, min(args.warmup, 3)), False)                                       # warm-up: scratch of the calls is allocated on first use
+    e2e_s, last_buf = e2e_loop(e2e_steps, False)
+    crc = zlib.crc32(hosts[last_buf].numpy().tobytes()) if rank == 0 else 0             # the frame the e2e loop left in host memory
+    e2e_moving_s, _ = e2e_loop(e2e_steps, True)
+    plan_ms = float(np.median(moving["plan_ms"])) if moving["plan_ms"] else 0.0
+
+    # ---- the fast build next to the parity build (N = 1): same frame, BZ_MODE_FAST ----
+    fast = None
+    if world == 1 and args.mode == "exact":
+        exact_frame = torch.zeros((height, width, 4), dtype=torch.uint8, device=dev)
+        fast_frame = torch.zeros_like(exact_frame)
+        lens.render_device(cam, scene, exact_frame)
+        lens.set_mode(fast_mode)
+        fast_stats = torch.zeros(len(bz.STAT_NAMES), dtype=torch.int64, device=dev)
+        fast_ms, fast_kernel = [], []
+        for k in range(2 + min(args.steps, 8)):
+            flush.fill_(1)
+            b, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            b.record()
+            lens.render_device(cam, scene, fast_frame, stats=fast_stats if k == 2 else None)
+            e.record()
+            torch.cuda.synchronize()
+            if k >= 2:
+                fast_ms.append(b.elapsed_time(e))
+                fast_kernel.append(lens.last_kernel_ms())
+        lens.set_mode(exact_mode)
+        diff = (exact_frame[..., 0].to(torch.int16) - fast_frame[..., 0].to(torch.int16)).abs()
+        fw = dict(zip(bz.STAT_NAMES, [int(x) for x in fast_stats.tolist()]))
+        fast = {"mode": "BZ_MODE_FAST: FMA contraction, MUFU reciprocal / rsqrt, FP32 cos2; ray generation and shading unchanged",
+                "value": frame_rays / (sum(fast_ms) / len(fast_ms) * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": sum(fast_ms) / len(fast_ms),
+                "kernel_ms": sum(fast_kernel) / len(fast_kernel),
+                "flop": FLOP_STAGE_A * fw["stage_a"] + FLOP_STAGE_B * fw["stage_b"] + FLOP_SNELL * fw["snell"],
+                "pixels_identical_pct": 100.0 * float((diff == 0).sum().item()) / diff.numel(), "pixels_differing": int((diff != 0).sum().item()),
+                "max_abs_diff": int(diff.max().item()), "one_sample_flip": (230 - 25) / spp,
+                "note": "the path amplifies rounding: the reference itself rebuilt with FMA contraction (-march=haswell) differs from the reference as much (DESIGN.md); "
+                        "north_star's 1e-5 tolerance is met only by the bit-exact parity build, which stays the headline"}
 
     if rank == 0:
         peak_tf, _ = bz.fp32_peak_probe(local)
@@ -299,34 +374,47 @@ def main_ours(args, name):
         hbm_bytes = own_pixels * (BYTES_PER_PIXEL_OUT + BYTES_PER_PIXEL_ACCUM)
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         achieved_tf = flop / (k_ms * 1e-3) / 1e12
+        sm_max = (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz", 1965.0)
+        nominal_tf = lens.info()["sm_count"] * 128 * 2 * sm_max * 1e6 / 1e12
         roofline = {
-            "bound": "fp32_alu", "kernel": "bz_warp_trace_kernel<RENDER> (packet walk; kernel_ms also holds bz_sky_kernel, 0.5 of 18.6 ms on cfg4)", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-            "frac": achieved_tf / peak_tf, "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_source,
+            "bound": "fp32_alu", "kernel": "bz_warp_trace_kernel<RENDER> (kernel_ms = the trace kernels + bz_sky_kernel of one step, CUDA events on the launching stream)",
+            "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
+            "peak_nominal": nominal_tf, "frac_of_nominal": achieved_tf / nominal_tf,
+            "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_source,
             "frac_of_no_fma_ceiling": achieved_tf / (peak_tf / 2.0),
             "no_fma_note": "the parity build has no FMA contraction (bit-exact with the reference's x86 build): one flop per lane and instruction, half the probe's peak",
-            "peak_source": "dependent-FMA probe kernel in this process (2 flop/lane/instr); nominal 148 SM x 128 lanes x 2 x %.0f MHz = %.1f"
-                           % (peaks.get("sm_max_mhz", 1965.0), 148 * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12),
+            "peak_source": "FMA probe kernel in this process (16 independent chains per thread, 2 flop/lane/instr); peak_nominal = SMs x 128 lanes x 2 x %.0f MHz" % sm_max,
             "flop_model": "33 x stage_a + 1750 x stage_b + 45 x snell, executed counts (not brute-force-equivalent)",
             "kernel_ms": k_ms, "stage_a": own["stage_a"], "stage_b": own["stage_b"], "snell": own["snell"], "node_visits": own["node_visits"],
             "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / (k_ms * 1e-3) / 1e9, "peak_gbs": hbm_peak,
                     "frac": hbm_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback"},
         }
-        launches_per_step = lens.last_kernel_launches() + (1 if world > 1 else 0)       # sky + trace + resolve (+ assemble on rank 0)
+        if fast is not None:
+            fast["roofline_frac"] = fast.pop("flop") / (fast["kernel_ms"] * 1e-3) / 1e12 / peak_tf
+            fast["roofline_frac_of_nominal"] = fast["roofline_frac"] * peak_tf / nominal_tf
         line = {
             "metric": "Mrays/s", "value": frame_rays / (ms_per_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": name, "patches": lens.patch_count, "image": "%dx%d" % (width, height), "spp": spp, "primary_rays_per_step": frame_rays,
                        "refractive_index": spec["ri"], "max_crossings": spec["max_crossings"], "parallelism": "row stripes of %d x %d ranks" % (stripe, world),
-                       "l2": "flushed between steps (256 MiB fill)", "mode": "culled (exact candidate-set-preserving BVH)" + (", BZ_MODE_FAST arithmetic" if args.mode == "fast" else ""), "fmad": args.mode == "fast", "pipeline": args.pipeline,
-                       "setup_s": setup_s},
+                       "l2": "flushed between steps (256 MiB fill, outside the per-step event pairs; flush_ms says what it costs)",
+                       "mode": "culled (exact candidate-set-preserving BVH)" + (", BZ_MODE_FAST arithmetic" if args.mode == "fast" else ""), "fmad": args.mode == "fast",
+                       "pipeline": args.pipeline, "setup_s": setup_s},
+            "flush_ms": flush_ms, "wall_ms_per_step_with_flush": (wall1 - wall0) / args.steps * 1e3,
             "e2e": {"value": frame_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(bz.load().bz_sizeof_camera() + bz.load().bz_sizeof_scene()),
                     "d2h_bytes_per_step": width * height * 4, "ms_per_step": e2e_s * 1e3,
-                    "call": "bz_render_host into pinned host memory" if world == 1 else "bz_render_striped + NCCL all-gather + bz_assemble_stripes + D2H to pinned host"},
+                    "call": "bz_render_host into pinned host memory" if world == 1 else
+                            "bz_render_striped on the compute stream; bz_gather_rows (NCCL send / recv to rank 0) + assembly + D2H to pinned host on a side stream, double-buffered"},
+            "e2e_moving_camera": {"value": frame_rays / e2e_moving_s / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_moving_s * 1e3, "plan_ms": plan_ms,
+                                  "note": "the eye moves by one ulp every step: every frame is planned anew (bz_plan_tiles on the host + upload of the tile list)"},
+            "frame_crc32": "%08x" % crc,
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks, "roofline": roofline, "work_per_step": work,
             "refract_calls_per_s": work["refract_calls"] / (ms_per_step * 1e-3),
         }
+        if fast is not None:
+            line["fast"] = fast
         if not args.no_cpu_baseline and world == 1:
             threads = host_cores()
             ref = reference_sample(name, args.cpu_seconds, threads)
@@ -337,6 +425,7 @@ def main_ours(args, name):
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
+        comm.close()
         dist.destroy_process_group()
 
 

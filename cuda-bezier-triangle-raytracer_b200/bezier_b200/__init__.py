@@ -146,6 +146,10 @@ SIGNATURES = {
     "bz_striped_rows": (_u32, [_u32, _u32, _u32, _u32]),
     "bz_render_striped": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _u32, _vp, _vp, _vp]),
     "bz_assemble_stripes": (_int, [_vp, _u32, _u32, _u32, _u32, _u32, _vp, _vp]),
+    "bz_comm_unique_id": (_int, [_vp]),
+    "bz_comm_create": (_int, [_vp, _u32, _u32, _int, C.POINTER(_vp)]),
+    "bz_comm_destroy": (_int, [_vp]),
+    "bz_gather_rows": (_int, [_vp, _vp, _u32, _u32, _u32, _u32, _vp, _vp]),
     "bz_fp32_peak_probe": (_int, [_int, C.POINTER(_f), C.POINTER(_f)]),
     "bz_mesh_create": (_int, [C.POINTER(_vp)]),
     "bz_mesh_destroy": (_int, [_vp]),
@@ -543,6 +547,40 @@ class BezierLens:
     def render_striped_device(self, camera, scene, stripe_rows, rank, ranks, rgba, stats=None, stream=None):
         _check(self.lib.bz_render_striped(self.h, C.byref(camera), C.byref(scene), stripe_rows, rank, ranks, _ptr(rgba), _ptr(stats),
                                           _stream_handle(stream)))
+
+
+class Comm:
+    """bz_comm: the NCCL communicator of the image gather (include/bz_capi.h).  `share_id(id_bytes or None) -> id_bytes` ships the
+    128-byte id from rank 0 to every rank (torch.distributed broadcast in sharding.make_comm, MPI, a file ...)."""
+
+    def __init__(self, rank, ranks, device, share_id):
+        self.lib = load()
+        self.rank, self.ranks, self.device = rank, ranks, device
+        ident = None
+        if rank == 0:
+            buf = (C.c_uint8 * 128)()
+            _check(self.lib.bz_comm_unique_id(C.byref(buf)))
+            ident = bytes(buf)
+        ident = share_id(ident)
+        assert len(ident) == 128
+        handle = _vp()
+        _check(self.lib.bz_comm_create((C.c_uint8 * 128).from_buffer_copy(ident), rank, ranks, device, C.byref(handle)))
+        self.h = handle
+
+    def gather_rows(self, band, width, height, stripe_rows, rgba=None, root=0, stream=None):
+        """every rank: its stripe band (device tensor); root: `rgba` [height, width, 4] gets the assembled frame"""
+        _check(self.lib.bz_gather_rows(self.h, _ptr(band), width, height, stripe_rows, root, _ptr(rgba), _stream_handle(stream)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.bz_comm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def assemble_stripes_device(bands, band_rows, width, height, stripe_rows, ranks, rgba, stream=None):

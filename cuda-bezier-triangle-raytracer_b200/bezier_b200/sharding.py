@@ -29,3 +29,20 @@ def gather_bands(band, bands_out=None):
         bands_out = torch.empty((world,) + tuple(band.shape), dtype=band.dtype, device=band.device)
     dist.all_gather_into_tensor(bands_out.view((-1,) + tuple(band.shape[1:])), band)    # concatenated along dim 0
     return bands_out
+
+
+def make_comm(bz, device):
+    """bz.Comm over the ranks of the initialised torch.distributed group: torch only carries the 128-byte id (bootstrap), the
+    gather itself is bz_gather_rows in the C ABI (ncclSend / ncclRecv to the root)"""
+    import torch
+    import torch.distributed as dist
+    rank, world = (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
+
+    def share(ident):
+        if world == 1:
+            return ident
+        box = [ident]
+        dist.broadcast_object_list(box, src=0)
+        return box[0]
+
+    return bz.Comm(rank, world, device, share)

@@ -30,6 +30,7 @@ extern "C" {
 #define BZ_ERR_NO_DEVICE     -3   /* no usable CUDA device: there is no CPU path */
 #define BZ_ERR_PREPROCESS    -4   /* mesh preprocessing threw (e.g. "Vertex on edge detected.", reference/mesh.cpp:204) */
 #define BZ_ERR_OVERFLOW      -5   /* a device-side work list overflowed (bz_lens_check) */
+#define BZ_ERR_COMM          -6   /* NCCL missing or failing (bz_comm_*, bz_gather_rows) */
 
 /* RefractionResult, reference/bezierLens.h:7-11 */
 #define BZ_STATUS_NONE        0u
@@ -230,6 +231,21 @@ int  bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scen
 uint32_t bz_striped_rows(uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t ranks);
 int  bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t stripe_rows, uint32_t rank,
                        uint32_t ranks, uint8_t *d_rgba, bz_stats *d_stats, void *stream);
+
+/* The image gather of the row-sharded render (north_star subsystem 4: "NCCL gather over NVLink"; SURVEY.md section 8(b): bz_gather_rows).
+ * One process per GPU.  Rank 0 makes an id (bz_comm_unique_id) and ships its 128 bytes to the other ranks by any means (MPI, a socket,
+ * a file, torch.distributed); every rank then calls bz_comm_create with its rank -- a collective call (ncclCommInitRank).  NCCL is
+ * loaded at run time; without it these calls return BZ_ERR_COMM and everything else still works.
+ * bz_gather_rows: every rank passes its band of bz_render_striped (bz_striped_rows(height, stripe_rows, rank, ranks) rows); the root
+ * receives the bands over NVLink / NVSwitch (ncclSend / ncclRecv, one group) and assembles d_rgba = height x width x 4 bytes in image
+ * order; d_rgba is ignored on the other ranks.  Asynchronous on `stream` on every rank. */
+#define BZ_COMM_ID_BYTES 128
+typedef struct bz_comm bz_comm;
+int  bz_comm_unique_id(uint8_t out_id[BZ_COMM_ID_BYTES]);
+int  bz_comm_create(const uint8_t id[BZ_COMM_ID_BYTES], uint32_t rank, uint32_t ranks, int device, bz_comm **out_comm);
+int  bz_comm_destroy(bz_comm *comm);
+int  bz_gather_rows(bz_comm *comm, const uint8_t *d_band, uint32_t width, uint32_t height, uint32_t stripe_rows, uint32_t root,
+                    uint8_t *d_rgba, void *stream);
 
 /* After an all-gather of the ranks' stripe buffers (each padded to band_rows rows; NCCL over NVLink in bench.py):
  * d_bands = ranks x band_rows x width x 4 bytes -> d_rgba = height x width x 4 bytes in image order. */

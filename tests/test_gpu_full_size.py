@@ -10,7 +10,7 @@ import common
 pytestmark = pytest.mark.gpu
 
 #            workload                          lattice step (pixels)
-CASES = [("cfg1_sphere_640x480", 4), ("cfg2_ellipsoid64x32_1080p", 12), ("cfg3_robot_1080p", 6), ("cfg4_freeform181x91_4k_16spp", 96)]
+CASES = [("cfg1_sphere_640x480", 4), ("cfg2_ellipsoid64x32_1080p", 12), ("cfg3_robot_1080p", 6), ("cfg4_freeform181x91_4k_16spp", 32)]
 
 
 @pytest.mark.parametrize("name,step", CASES)
@@ -35,7 +35,7 @@ def test_full_frame_matches_reference_on_a_pixel_lattice(oracle_built, name, ste
     _, rmesh, rcam_kw, rscene_kw = workloads.setup(name, bzref.RefMesh)
     ref_lens = bzref.RefLens(spec["ri"], bzref.RefBezierMesh(rmesh))
     rcam, rscene = bzref.make_camera(w, h, **rcam_kw), bzref.make_scene(**rscene_kw)
-    ref, ref_stats, rays = ref_lens.render(rcam, rscene, pixel_step=step, threads=16)
+    ref, ref_stats, rays = ref_lens.render(rcam, rscene, pixel_step=step, threads=16)      # cfg4: 8 160 pixels x 16 samples
     lattice = (slice(0, h, step), slice(0, w, step))
     assert rays == len(range(0, h, step)) * len(range(0, w, step)) * spp
     diff = int((ref[lattice] != rgba[lattice]).any(-1).sum())
@@ -63,3 +63,24 @@ def test_cfg4_stripes_equal_whole_frame(oracle_built):
     bz.assemble_stripes_device(bands, reserve, cam.width, cam.height, stripe, ranks, image)
     torch.cuda.synchronize()
     assert np.array_equal(image.cpu().numpy(), full)
+
+
+def test_gather_rows_through_the_c_abi_single_rank(oracle_built):
+    """bz_comm_* + bz_gather_rows (NCCL loaded at run time) with a communicator of one rank: the root's own band goes through the
+    same staging and assembly as the received ones.  Several ranks are exercised by bench.py under torchrun, whose frame_crc32
+    must equal the single-GPU one (profiles/, SCALE); the stripe arithmetic itself is covered on the CPU (tests/test_sharding_gloo.py)."""
+    import torch
+    import bezier_b200 as bz
+    from bezier_b200 import workloads
+    spec, mesh, cam_kw, scene_kw = workloads.setup("cfg1_sphere_640x480", bz.Mesh)
+    lens = bz.BezierLens(spec["ri"], bz.BezierMesh(mesh))
+    cam, scene = bz.make_camera(spec["width"], spec["height"], **cam_kw), bz.make_scene(**scene_kw)
+    full, _ = lens.render(cam, scene)
+    comm = bz.Comm(0, 1, 0, lambda ident: ident)
+    band = torch.zeros((cam.height, cam.width, 4), dtype=torch.uint8, device="cuda")
+    image = torch.zeros_like(band)
+    lens.render_striped_device(cam, scene, workloads.STRIPE_ROWS, 0, 1, band)
+    comm.gather_rows(band, cam.width, cam.height, workloads.STRIPE_ROWS, rgba=image)
+    torch.cuda.synchronize()
+    assert np.array_equal(image.cpu().numpy(), full)
+    comm.close()
