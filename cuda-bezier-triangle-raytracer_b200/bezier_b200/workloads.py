@@ -11,7 +11,7 @@ checker background 6 s behind the box with cells of 0.5 s.
 import os
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-ROBOT_STL = os.path.join(ROOT, "tests", "golden", "robot.stl")
+ROBOT_STL = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "data", "robot.stl")      # BASELINE.json config 3 names this file (reference/robot.stl)
 
 WORKLOADS = {
     # name: mesh recipe, image, strata (spp = strata^2), refractive index, max surface crossings

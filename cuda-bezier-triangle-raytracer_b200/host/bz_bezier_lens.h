@@ -9,6 +9,7 @@
 #define BZ_BEZIER_LENS_H
 
 #include <cstdint>
+#include <memory>
 #include <stdexcept>
 #include <string>
 #include <utility>
@@ -45,14 +46,20 @@ struct BezierIntersection final {
 
 class BezierLens final {
 public:
-  // BezierLens(float aRi, BezierMesh const&), reference/bezierLens.h:23
+  // BezierLens(float aRi, BezierMesh const&) and BezierLens(float aRi, BezierMesh &&), reference/bezierLens.h:23-24.  The reference's
+  // lens owns a copy of the mesh; here it owns the device tables made from it, and copies of a lens SHARE them (they are
+  // read-only, and every call works in a per-stream / per-call context of the handle: include/bz_capi.h "Threads and streams").
   BezierLens(float const aRi, BezierMesh const &aMesh, int const aDevice = 0) : mRefractiveIndex(aRi), mPatchCount(static_cast<uint32_t>(aMesh.size())) {
-    check(bz_lens_create(aMesh.records(), mPatchCount, aRi, aDevice, &mLens));
+    bz_lens *lens = nullptr;
+    check(bz_lens_create(aMesh.records(), mPatchCount, aRi, aDevice, &lens));
+    mShared = std::shared_ptr<bz_lens>(lens, [](bz_lens *aLens) { bz_lens_destroy(aLens); });
   }
-  ~BezierLens() { bz_lens_destroy(mLens); }
-  BezierLens(BezierLens &&aOther) noexcept : mRefractiveIndex(aOther.mRefractiveIndex), mPatchCount(aOther.mPatchCount), mLens(aOther.mLens) { aOther.mLens = nullptr; }
-  BezierLens(BezierLens const &) = delete;
-  BezierLens &operator=(BezierLens const &) = delete;
+  BezierLens(float const aRi, BezierMesh &&aMesh, int const aDevice = 0) : BezierLens(aRi, static_cast<BezierMesh const &>(aMesh), aDevice) {}
+  BezierLens(BezierLens const &) = default;
+  BezierLens(BezierLens &&) noexcept = default;
+  BezierLens &operator=(BezierLens const &) = default;
+  BezierLens &operator=(BezierLens &&) noexcept = default;
+  ~BezierLens() = default;
 
   // std::pair<Ray, RefractionResult> refract(Ray const&, RefractionResult aExpected) const, reference/bezierLens.h:27.
   // On cNone the returned ray is the incoming one (the reference leaves it partly uninitialised).
@@ -61,7 +68,7 @@ public:
     uint32_t const expected = static_cast<uint32_t>(aExpected);
     float outStart[3], outDir[3];
     uint32_t status = 0u;
-    check(bz_refract_batch_host(mLens, start, dir, &expected, 1u, outStart, outDir, &status, nullptr));
+    check(bz_refract_batch_host(mShared.get(), start, dir, &expected, 1u, outStart, outDir, &status, nullptr));
     Ray result;
     result.mStart = Vec3{outStart[0], outStart[1], outStart[2]};
     result.mDirection = Vec3{outDir[0], outDir[1], outDir[2]};
@@ -71,7 +78,7 @@ public:
   // the same over n host rays (3 floats each); results in caller-owned arrays, aOutPatch may be null
   void refract(float const *aStart, float const *aDirection, uint32_t const *aExpected, uint64_t const aCount,
                float *aOutStart, float *aOutDirection, uint32_t *aOutStatus, uint32_t *aOutPatch = nullptr) const {
-    check(bz_refract_batch_host(mLens, aStart, aDirection, aExpected, aCount, aOutStart, aOutDirection, aOutStatus, aOutPatch));
+    check(bz_refract_batch_host(mShared.get(), aStart, aDirection, aExpected, aCount, aOutStart, aOutDirection, aOutStatus, aOutPatch));
   }
 
   // BezierIntersection BezierMesh::intersect(Ray const&) const, reference/bezierMesh.h:37
@@ -79,7 +86,7 @@ public:
     float const start[3] = { aRay.mStart.x, aRay.mStart.y, aRay.mStart.z }, dir[3] = { aRay.mDirection.x, aRay.mDirection.y, aRay.mDirection.z };
     uint32_t what = 0u, patch = 0u;
     float distance = 0.0f, cosine = 0.0f, point[3], normal[3], bary[3];
-    check(bz_intersect_batch_host(mLens, start, dir, 1u, &what, &patch, &distance, point, normal, &cosine, bary));
+    check(bz_intersect_batch_host(mShared.get(), start, dir, 1u, &what, &patch, &distance, point, normal, &cosine, bary));
     BezierIntersection result;
     result.mWhat = static_cast<BezierIntersection::What>(what);
     result.mValid = (what == BZ_WHAT_INTERSECT);
@@ -94,22 +101,22 @@ public:
 
   // headless render of rows [aRow0, aRow1) into a host RGBA8 buffer (definitions in include/bz_capi.h)
   void render(bz_camera const &aCamera, bz_scene const &aScene, uint32_t const aRow0, uint32_t const aRow1, uint8_t *aRgba, bz_stats *aStats = nullptr) const {
-    check(bz_render_host(mLens, &aCamera, &aScene, aRow0, aRow1, aRgba, aStats));
+    check(bz_render_host(mShared.get(), &aCamera, &aScene, aRow0, aRow1, aRgba, aStats));
   }
 
   // illumination mode (README.md:161-194): emitter -> lens -> counting bins of a target rectangle, host bins are accumulated into
   void illuminate(bz_emitter const &aEmitter, bz_target const &aTarget, uint32_t const aMaxCrossings, uint32_t *aBins, bz_stats *aStats = nullptr) const {
-    check(bz_illuminate_host(mLens, &aEmitter, &aTarget, aMaxCrossings, aBins, aStats));
+    check(bz_illuminate_host(mShared.get(), &aEmitter, &aTarget, aMaxCrossings, aBins, aStats));
   }
 
   float getRefractiveIndex() const { return mRefractiveIndex; }
   uint32_t size() const { return mPatchCount; }
-  bz_lens *handle() const { return mLens; }       // for the device-pointer entry points of the C ABI
+  bz_lens *handle() const { return mShared.get(); }       // for the device-pointer entry points of the C ABI
 
 private:
   float    mRefractiveIndex;
   uint32_t mPatchCount;
-  bz_lens *mLens = nullptr;
+  std::shared_ptr<bz_lens> mShared;      // copies of a lens share the device tables
 
   static void check(int const aCode) {
     if(aCode != BZ_OK) { throw std::runtime_error("libbz_b200 error " + std::to_string(aCode) + ": " + bz_last_error()); }

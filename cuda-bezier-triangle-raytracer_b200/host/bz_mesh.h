@@ -59,6 +59,20 @@ public:
   // per vertex index, with a lookup by vertex value.  Throws std::out_of_range like .at() does
   // (bezierMesh.cpp:17-18) when standardizeNormals() has not run or the vertex is unknown.
   Vector const &getAverageNormal(Vertex const &aVertex) const;
+  // Vertex2averageNormals const &getVertex2averageNormals() const, reference/mesh.h:69: a read-only map view with the calls the
+  // reference's users make (bezierMesh.cpp:17-18: .at(vertex)); iteration goes over (vertex, normal) in first-seen order
+  class Vertex2averageNormals final {
+  public:
+    explicit Vertex2averageNormals(Mesh const &aMesh) : mMesh(aMesh) {}
+    Vector const &at(Vertex const &aVertex) const { return mMesh.getAverageNormal(aVertex); }      // throws std::out_of_range like unordered_map::at
+    size_t count(Vertex const &aVertex) const { return mMesh.mNormalIndex.count(aVertex); }
+    size_t size() const { return mMesh.mVertexNormals.size(); }
+    bool empty() const { return mMesh.mVertexNormals.empty(); }
+    std::pair<Vertex const &, Vector const &> operator[](size_t const aI) const { return { mMesh.mUniqueVertices[aI], mMesh.mVertexNormals[aI] }; }
+  private:
+    Mesh const &mMesh;
+  };
+  Vertex2averageNormals getVertex2averageNormals() const { return Vertex2averageNormals(*this); }
   std::vector<Vertex> const &getUniqueVertices() const { return mUniqueVertices; }   // first-seen order
   std::vector<Vector> const &getVertexNormals() const { return mVertexNormals; }     // same order
 

@@ -6,7 +6,7 @@ import subprocess
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-ROBOT_STL = os.path.join(ROOT, "tests", "golden", "robot.stl")
+ROBOT_STL = os.path.join(ROOT, "cuda-bezier-triangle-raytracer_b200", "data", "robot.stl")
 
 _cache = {}
 

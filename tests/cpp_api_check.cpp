@@ -15,6 +15,11 @@ int main(int argc, char **argv) {
   mesh.standardizeVertices();
   mesh.standardizeNormals();
   if(mesh.size() != 256u || mesh.getFace2neighbours().size() != 256u) { std::printf("bad mesh\n"); return 1; }
+  // Mesh::getVertex2averageNormals(), reference/mesh.h:69: a map view; .at() of a corner is what BezierMesh's constructor reads
+  auto const normals = mesh.getVertex2averageNormals();
+  if(normals.size() != mesh.getUniqueVertices().size() || normals.count(mesh[0u][0u]) != 1u) { std::printf("bad normal map\n"); return 1; }
+  bz::Vector const &corner = normals.at(mesh[0u][1u]);
+  if(std::fabs(corner.x * corner.x + corner.y * corner.y + corner.z * corner.z - 1.0f) > 1e-5f) { std::printf("normal not unit\n"); return 1; }
   bz::BezierMesh bezier(mesh);
   if(bezier.size() != 768u) { std::printf("bad bezier mesh\n"); return 1; }
   auto const neighbours = bezier[0u].getNeighbours();               // patch 0 neighbours {91, 1, 2}
@@ -42,8 +47,10 @@ int main(int argc, char **argv) {
     return 1;
   }
   try {
-    bz::BezierLens lens(1.3f, bezier);
+    bz::BezierLens original(1.3f, bz::BezierMesh(mesh));             // BezierLens(float, BezierMesh&&), reference/bezierLens.h:24
     if(!gpu) { std::printf("lens built without a device?\n"); return 1; }
+    bz::BezierLens lens(original);                                    // copies share the device tables (the reference copies the mesh)
+    { bz::BezierLens moved(std::move(original)); if(moved.handle() != lens.handle()) { std::printf("copy does not share\n"); return 1; } }
     bz::Ray ray(bz::Vec3{-10.0f, 0.1f, 0.2f}, bz::Vec3{2.0f, 0.0f, 0.0f});
     auto const hit = lens.intersect(ray);
     if(hit.mWhat != bz::BezierIntersection::What::cIntersect || hit.mPatch != 350u) { std::printf("bad hit %u\n", hit.mPatch); return 1; }
