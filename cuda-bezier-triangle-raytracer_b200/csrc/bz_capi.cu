@@ -515,7 +515,10 @@ static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<u
   };
   lens_tiles.clear();
   sky_tiles.clear();
+  lens_tiles.reserve((size_t)desc.tiles_x * desc.tiles_y);
+  sky_tiles.reserve((size_t)desc.tiles_x * desc.tiles_y);
   std::vector<uint32_t> weight;                         // per lens tile: outline boxes that project onto it
+  weight.reserve((size_t)desc.tiles_x * desc.tiles_y);
   for(uint32_t turn = 0u; turn < desc.tiles_y; ++turn) {
     uint32_t const ty = ((turn & 1u) == 0u) ? (turn >> 1) : (desc.tiles_y - 1u - (turn >> 1));     // rows from the outside in
     uint32_t const row_a = ty * side, row_b = std::min(row_a + side, desc.rows) - 1u;
@@ -530,11 +533,14 @@ static bool bz_plan_tiles(const bz_lens *lens, const bz_job &desc, std::vector<u
   // the tiles many boxes project onto (silhouette of the body: thick projections, grazing rays, the costliest packets of the
   // frame) are handed out first, so the persistent grid ends on cheap tiles; within a weight the outside-in order stays
   {
-    std::vector<uint32_t> index(lens_tiles.size());
-    for(uint32_t i = 0u; i < index.size(); ++i) { index[i] = i; }
-    std::stable_sort(index.begin(), index.end(), [&](uint32_t a, uint32_t b) { return weight[a] > weight[b]; });
+    // (a stable counting sort by descending weight: the plan is rebuilt for every frame of a moving camera)
+    uint32_t heaviest = 0u;
+    for(uint32_t w : weight) { heaviest = std::max(heaviest, w); }
+    std::vector<uint32_t> first(heaviest + 2u, 0u);
+    for(uint32_t w : weight) { ++first[heaviest - w + 1u]; }
+    for(uint32_t k = 1u; k < first.size(); ++k) { first[k] += first[k - 1u]; }
     std::vector<uint32_t> sorted(lens_tiles.size());
-    for(uint32_t i = 0u; i < index.size(); ++i) { sorted[i] = lens_tiles[index[i]]; }
+    for(size_t i = 0u; i < lens_tiles.size(); ++i) { sorted[first[heaviest - weight[i]]++] = lens_tiles[i]; }
     lens_tiles.swap(sorted);
   }
   return true;

@@ -616,14 +616,20 @@ __global__ void __launch_bounds__(256) bz_wave_resolve_kernel(const bz_tables T,
     }
   }
   if(J.stats != nullptr) {
+    // event counts: warp totals into shared memory, one atomic per counter and CTA (millions of rays end here per pass)
+    __shared__ uint32_t tally[4];
+    if(threadIdx.x < 4u) { tally[threadIdx.x] = 0u; }
+    __syncthreads();
     const uint32_t snell = __reduce_add_sync(0xffffffffu, events & 0xffu), entered = __reduce_add_sync(0xffffffffu, (events >> 8) & 0xffu);
     const uint32_t exited = __reduce_add_sync(0xffffffffu, (events >> 16) & 0xffu), lost = __reduce_add_sync(0xffffffffu, events >> 24);
     if((threadIdx.x & 31u) == 0u) {
-      if(snell != 0u) { atomicAdd(J.stats + BZC_SNELL, (unsigned long long)snell); }
-      if(entered != 0u) { atomicAdd(J.stats + BZC_ENTER, (unsigned long long)entered); }
-      if(exited != 0u) { atomicAdd(J.stats + BZC_EXIT, (unsigned long long)exited); }
-      if(lost != 0u) { atomicAdd(J.stats + BZC_LOST, (unsigned long long)lost); }
+      if(snell != 0u) { atomicAdd(&tally[0], snell); }
+      if(entered != 0u) { atomicAdd(&tally[1], entered); }
+      if(exited != 0u) { atomicAdd(&tally[2], exited); }
+      if(lost != 0u) { atomicAdd(&tally[3], lost); }
     }
+    __syncthreads();
+    if(threadIdx.x < 4u && tally[threadIdx.x] != 0u) { atomicAdd(J.stats + BZC_SNELL + threadIdx.x, (unsigned long long)tally[threadIdx.x]); }
   }
 }
 
