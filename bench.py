@@ -56,7 +56,7 @@ class ClockSampler:
     def __init__(self, device):
         self.rows, self.proc, self.thread = [], None, None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(device), "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(device), "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -72,14 +72,18 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
-        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.2 and len(r) >= 7] or [r for _, r in self.rows if len(r) >= 7]
+        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.1 and len(r) >= 7]
+        window = "timed region"
+        if not rows:                                            # a timed region shorter than the sampling period: the samples since the warm-up
+            rows, window = [r for _, r in self.rows if len(r) >= 7], "warm-up + timed region"
+
         if not rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
         sm = sorted(float(r[0]) for r in rows)
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
         reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "power_w_max": max(float(r[2]) for r in rows),
-                "samples": len(rows), "reasons": reasons}
+                "samples": len(rows), "window": window, "reasons": reasons}
 
 
 def host_cores():
@@ -217,10 +221,14 @@ def main_ours(args, name):
     hosts = [torch.empty((height, width, 4), dtype=torch.uint8).pin_memory() for _ in range(2)] if rank == 0 else [None, None]
     kernel_ms = []
 
+    rendered_events, split = [], {}
+
     def render_and_gather(buf, record):
         lens.render_striped_device(cam, scene, stripe, rank, world, bands[buf], stats=stats)
         if record:
             kernel_ms.append(lens.last_kernel_ms())                                     # events on the launching stream around the trace kernels
+            rendered_events.append(torch.cuda.Event(enable_timing=True))
+            rendered_events[-1].record()
         if world > 1:
             comm.gather_rows(bands[buf], width, height, stripe, rgba=images[buf])        # NCCL send / recv over NVLink + assembly on rank 0
 
@@ -243,16 +251,19 @@ def main_ours(args, name):
         barrier()
         wall1 = time.time()
         total = torch.tensor([sum(b.elapsed_time(e) for b, e in pairs)], dtype=torch.float64, device=dev)
+        if record and len(rendered_events) == steps:
+            split["render_ms"] = sum(b.elapsed_time(m) for (b, _), m in zip(pairs, rendered_events)) / steps      # this rank: memset + sky + trace + resolve
+            split["gather_ms"] = sum(m.elapsed_time(e) for (_, e), m in zip(pairs, rendered_events)) / steps      # this rank: wait for the slowest sender + transfer + assembly
         if world > 1:
             dist.all_reduce(total, op=dist.ReduceOp.MAX)
         return float(total.item()) / steps, wall0, wall1
 
+    sampler = ClockSampler(local) if rank == 0 else None                                # started before the warm-up: nvidia-smi needs a moment to come up
     for _ in range(args.warmup):
         flush.fill_(1)
         render_and_gather(0, False)
     barrier()
     stats.zero_()
-    sampler = ClockSampler(local) if rank == 0 else None
     ms_per_step, wall0, wall1 = timed_steps(args.steps, True)
     clocks = sampler.stop(wall0, wall1) if sampler else None
     fb, fe = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -401,7 +412,7 @@ def main_ours(args, name):
                        "l2": "flushed between steps (256 MiB fill, outside the per-step event pairs; flush_ms says what it costs)",
                        "mode": "culled (exact candidate-set-preserving BVH)" + (", BZ_MODE_FAST arithmetic" if args.mode == "fast" else ""), "fmad": args.mode == "fast",
                        "pipeline": args.pipeline, "setup_s": setup_s},
-            "flush_ms": flush_ms, "wall_ms_per_step_with_flush": (wall1 - wall0) / args.steps * 1e3,
+            "step_split_rank0": split, "flush_ms": flush_ms, "wall_ms_per_step_with_flush": (wall1 - wall0) / args.steps * 1e3,
             "e2e": {"value": frame_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(bz.load().bz_sizeof_camera() + bz.load().bz_sizeof_scene()),
                     "d2h_bytes_per_step": width * height * 4, "ms_per_step": e2e_s * 1e3,
                     "call": "bz_render_host into pinned host memory" if world == 1 else
