@@ -1,9 +1,10 @@
 """`-m gpu` parity tests: the CUDA path through the C ABI against the oracle.
 
-Tolerance: the kernels are built with -fmad=false and IEEE div/sqrt, so every comparison with the
+Tolerance: the parity kernels are built with -fmad=false and IEEE div/sqrt, so every comparison with the
 oracle (oracle/_ref = the compiled reference + the documented hoist, and oracle/bz_oracle.c) is
-BIT-EXACT -- stricter than north_star's 1e-5 relative / 1 LSB, which is what a future FMA build
-would be held to.
+BIT-EXACT -- stricter than north_star's 1e-5 relative / 1 LSB.  The render cases run through both
+pipelines (persistent kernel, wavefront kernels).  The fast build (BZ_MODE_FAST) has its own file and
+its own, looser, written tolerances: tests/test_gpu_fast.py.
 """
 import numpy as np
 import pytest
