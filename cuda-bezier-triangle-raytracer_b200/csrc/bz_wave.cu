@@ -38,7 +38,9 @@ namespace BZ_NS {
 #ifndef BZV_WALK_CTAS
 #define BZV_WALK_CTAS    3       // resident CTAs per SM the walk kernel is compiled for (register budget)
 #endif
+#ifndef BZV_EVAL_WARPS
 #define BZV_EVAL_WARPS   4
+#endif
 #ifndef BZV_EVAL_CTAS
 #define BZV_EVAL_CTAS    4
 #endif
