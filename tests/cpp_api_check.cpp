@@ -5,6 +5,8 @@
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
+#include <vector>
+#include <cuda_runtime.h>
 #include "bz_bezier_lens.h"
 #include "bz_hemisphere.h"
 
@@ -70,6 +72,24 @@ int main(int argc, char **argv) {
     uint64_t landed = 0u;
     for(uint32_t b : bins) { landed += b; }
     if(stats.primary_rays != 8192u || stats.entered == 0u || landed == 0u || landed > 8192u) { std::printf("bad illumination %llu\n", (unsigned long long)landed); return 1; }
+    // row-sharded render without PyTorch: communicator of one rank, this rank's stripes, gather + assembly on the root
+    {
+      bz_camera camera = { {-12.0f, 0.0f, 0.0f}, {1.0f, 0.0f, 0.0f}, {0.0f, 1.0f, 0.0f}, {0.0f, 0.0f, 1.0f}, 0.14f, 0.105f, 96u, 72u, 2u, 0u };
+      bz_scene scene = { {1.0f, 0.0f, 0.0f, 12.0f}, {0.0f, 1.0f, 0.0f}, {0.0f, 0.0f, 1.0f}, 1.0f, 25u, 230u, 0u, 2u };
+      std::vector<uint8_t> whole(96u * 72u * 4u), gathered(96u * 72u * 4u);
+      lens.render(camera, scene, 0u, 72u, whole.data());
+      uint8_t id[BZ_COMM_ID_BYTES];
+      bz_comm *comm = nullptr;
+      if(bz_comm_unique_id(id) != BZ_OK || bz_comm_create(id, 0u, 1u, 0, &comm) != BZ_OK) { std::printf("no communicator: %s\n", bz_last_error()); return 1; }
+      uint8_t *dBand = nullptr, *dImage = nullptr;
+      if(cudaMalloc((void**)&dBand, whole.size()) != cudaSuccess || cudaMalloc((void**)&dImage, whole.size()) != cudaSuccess) { std::printf("cudaMalloc failed\n"); return 1; }
+      int rc = bz_render_striped(lens.handle(), &camera, &scene, 8u, 0u, 1u, dBand, nullptr, nullptr);
+      if(rc == BZ_OK) { rc = bz_gather_rows(comm, dBand, camera.width, camera.height, 8u, 0u, dImage, nullptr); }
+      if(rc != BZ_OK || cudaMemcpy(gathered.data(), dImage, gathered.size(), cudaMemcpyDeviceToHost) != cudaSuccess) { std::printf("gather failed: %s\n", bz_last_error()); return 1; }
+      if(gathered != whole) { std::printf("gathered frame differs\n"); return 1; }
+      cudaFree(dBand); cudaFree(dImage);
+      bz_comm_destroy(comm);
+    }
     std::printf("ok gpu\n");
   }
   catch(std::runtime_error const &e) {

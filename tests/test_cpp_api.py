@@ -11,8 +11,10 @@ PKG = os.path.join(common.ROOT, "cuda-bezier-triangle-raytracer_b200")
 
 def build(tmp_path):
     exe = str(tmp_path / "cpp_api_check")
-    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(PKG, "host"), "-I" + os.path.join(common.ROOT, "include"),
-                           os.path.join(common.ROOT, "tests", "cpp_api_check.cpp"), "-L" + PKG, "-lbz_b200", "-Wl,-rpath," + PKG, "-o", exe])
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(PKG, "host"), "-I" + os.path.join(common.ROOT, "include"), "-I" + os.path.join(cuda, "include"),
+                           os.path.join(common.ROOT, "tests", "cpp_api_check.cpp"), "-L" + PKG, "-lbz_b200", "-L" + os.path.join(cuda, "lib64"), "-lcudart",
+                           "-Wl,-rpath," + PKG, "-Wl,-rpath," + os.path.join(cuda, "lib64"), "-o", exe])
     return exe
 
 

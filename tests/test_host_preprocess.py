@@ -169,3 +169,28 @@ def test_no_cpu_fallback_without_device():
     with pytest.raises(bz.BezierError) as e:
         bz.BezierLens(1.3, np.zeros((0, 64), np.float32))
     assert e.value.code == bz.ERR_NO_DEVICE
+
+
+def test_lens_create_rejects_bad_neighbour_indices():
+    """the follow hop indexes the device tables with the neighbour indices (bezierMesh.cpp:213-217): a record whose neighbour lies
+    outside the table is refused before anything is uploaded (checked without a device)"""
+    import bezier_b200 as bz
+    mesh = bz.Mesh().make_unit_sphere(8, 4)
+    mesh.standardize_vertices().standardize_normals()
+    table = bz.BezierMesh(mesh).patches().copy()
+    table.view(np.uint32)[5, 17] = table.shape[0]            # words 16..18 hold the neighbours
+    with pytest.raises(bz.BezierError) as e:
+        bz.BezierLens(1.3, table)
+    assert e.value.code == bz.ERR_INVALID and "neighbour" in str(e.value)
+
+
+def test_comm_argument_checks():
+    import ctypes as C
+    import bezier_b200 as bz
+    lib = bz.load()
+    handle = C.c_void_p()
+    ident = (C.c_uint8 * 128)()
+    assert lib.bz_comm_create(ident, 3, 2, 0, C.byref(handle)) == bz.ERR_INVALID      # rank >= ranks
+    assert lib.bz_comm_create(None, 0, 1, 0, C.byref(handle)) == bz.ERR_INVALID
+    assert lib.bz_gather_rows(None, None, 4, 4, 8, 0, None, None) == bz.ERR_INVALID
+    assert lib.bz_comm_destroy(None) == bz.OK
