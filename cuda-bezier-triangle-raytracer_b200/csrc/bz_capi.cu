@@ -48,8 +48,10 @@ int bz_fail(int code, const std::string &text) {
 #define BZ_CUDA(call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) { \
   return bz_fail(BZ_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while(0)
 
-#define BZ_WAVE_RAYS   (16u << 20)     // default chunk: kernel boundaries cost ~30 us each (the grid drains), so chunks are large
-#define BZ_WAVE_CANDS  4u
+#define BZ_WAVE_RAYS   (64u << 20)     // default chunk: every kernel boundary costs ~40 us of drained grid, so a frame is one chunk when it fits
+#define BZ_WAVE_CANDS  3u              // candidates reserved per ray slot (the 4K headline frame needs 1.45)
+#define BZ_WAVE_AUTO_RAYS (4ull << 20) // BZ_PIPELINE_AUTO: frames with at least this many ray slots on lens tiles ...
+#define BZ_WAVE_AUTO_CROSSINGS 4u      // ... and at most this many crossings (three kernel launches each) take the wavefront pipeline
 
 struct bz_lens;
 
@@ -362,7 +364,7 @@ int bz_lens_check(bz_lens *lens) {
     }
   }
   if(overflowed) {
-    return bz_fail(BZ_ERR_OVERFLOW, "candidate list of the wavefront pipeline overflowed (more than 4 stage-A survivors per ray over a whole chunk): the last frames are incomplete; "
+    return bz_fail(BZ_ERR_OVERFLOW, "candidate list of the wavefront pipeline overflowed (more than 3 stage-A survivors per ray over a whole chunk): the last frames are incomplete; "
                                     "render with bz_lens_set_pipeline(lens, BZ_PIPELINE_PERSISTENT)");
   }
   return BZ_OK;
@@ -710,9 +712,17 @@ static int bz_run(bz_context *ctx, int job, bz_job &desc) {
     bz_tables tables = lens->tables;
     if(lens->mode == BZ_MODE_LANES) { tables.packet_count = 0u; }
     if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, ctx->d_tiles + desc.tile_count, sky_count, stream)); ++ctx->launches; }
-    // RENDER: the wavefront pipeline when asked for; measured on the 4K frame the two are level (17.8 ms each), so
-    // BZ_PIPELINE_AUTO keeps the persistent kernel, which needs no ray / candidate buffers
-    bool const wavefront = job == BZ_JOB_RENDER && lens->mode != BZ_MODE_LANES && grid != 0 && lens->pipeline == BZ_PIPELINE_WAVEFRONT;
+    // RENDER: the wavefront pipeline when asked for.  BZ_PIPELINE_AUTO takes it where it measured faster: the
+    // parity build, large frames, few crossings -- and only while its ray / candidate lists fit comfortably into free device memory.
+    bool wavefront = job == BZ_JOB_RENDER && lens->mode != BZ_MODE_LANES && grid != 0 && lens->pipeline == BZ_PIPELINE_WAVEFRONT;
+    if(job == BZ_JOB_RENDER && lens->pipeline == BZ_PIPELINE_AUTO && lens->mode == BZ_MODE_CULLED && grid != 0) {
+      uint64_t const slots = desc.tile_count * (uint64_t)(((desc.tile_rays + 31u) / 32u) * 32u);
+      if(slots >= BZ_WAVE_AUTO_RAYS && desc.scene.max_crossings <= BZ_WAVE_AUTO_CROSSINGS) {
+        uint64_t const need = std::min<uint64_t>(slots, lens->wave_chunk) * (36u + 52u * BZ_WAVE_CANDS);
+        size_t free_bytes = 0u, total_bytes = 0u;
+        wavefront = ctx->wave_bytes >= need || (cudaMemGetInfo(&free_bytes, &total_bytes) == cudaSuccess && need <= free_bytes / 4u);
+      }
+    }
     if(wavefront) {
       int rc = bz_run_wave(ctx, desc);
       if(rc != BZ_OK) { return rc; }

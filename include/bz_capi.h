@@ -169,14 +169,16 @@ int  bz_lens_patch_count(const bz_lens *lens, uint32_t *out_count);
 /* How bz_render* runs the tiles that can meet the lens (BZ_MODE_CULLED / BZ_MODE_FAST; the results are the same bits):
  *   BZ_PIPELINE_PERSISTENT  one persistent warp-scheduled kernel does walk, stage A, stage B and resolve (csrc/bz_trace.cu)
  *   BZ_PIPELINE_WAVEFRONT   three kernels per surface crossing over global ray / candidate lists (csrc/bz_wave.cu)
- *   BZ_PIPELINE_AUTO        the default: the persistent kernel (on the 4K headline frame the two are level; the wavefront pipeline
- *                           needs 36 bytes per ray slot + 208 bytes of candidate list per ray slot of device memory)
+ *   BZ_PIPELINE_AUTO        the default: the wavefront kernels for frames of the parity build with at least 4 Mi ray slots on lens tiles and
+ *                           at most 4 crossings, while their lists (36 bytes per ray slot + 3 x 52 bytes of candidate list per slot; 8.6 GB
+ *                           for the 4K x 16 spp headline frame) fit into a quarter of the free device memory; else the persistent kernel
  * The batch entry points (bz_refract_batch, bz_intersect_batch, bz_trace_to_target) always use the persistent kernel. */
 #define BZ_PIPELINE_AUTO        0u
 #define BZ_PIPELINE_PERSISTENT  1u
 #define BZ_PIPELINE_WAVEFRONT   2u
 int  bz_lens_set_pipeline(bz_lens *lens, uint32_t pipeline);
-/* Ray slots per chunk of the wavefront pipeline (device memory: 36 bytes per slot + 4 x 52 bytes of candidate list per slot). */
+/* Ray slots per chunk of the wavefront pipeline (default 64 Mi: a frame is one chunk when it fits; device memory: 36 bytes per slot +
+ * 3 x 52 bytes of candidate list per slot, allocated for the largest chunk a context has seen). */
 int  bz_lens_set_wave_chunk(bz_lens *lens, uint32_t ray_slots);
 /* Synchronises with the work in flight on the handle and reports (once) a device-side overflow of the wavefront pipeline's
  * candidate list as BZ_ERR_OVERFLOW; the *_host render calls do this themselves. */
