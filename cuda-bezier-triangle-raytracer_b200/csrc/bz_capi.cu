@@ -87,10 +87,13 @@ struct bz_context {
   cudaEvent_t ev_tiles;               // the last upload out of h_tiles has been consumed
   double     plan_ms;                 // host time of the most recent call's bz_plan_tiles + upload (0: the kept plan was used)
   uint32_t   launches;                // kernels of the most recent call
-  // RENDER, wavefront pipeline (csrc/bz_wave.cu): ray slots and candidate list of one chunk of tiles
-  bz_wave    wave;
-  void      *d_wave;                  // one allocation behind the pointers of `wave`
+  // RENDER, wavefront pipeline (csrc/bz_wave.cu): two sets of ray slots + candidate list, each with a stream of its own -- the chunks of a
+  // frame alternate between them, so that one chunk's kernels fill the drained grid at the other's kernel boundaries
+  bz_wave    wave[2];
+  void      *d_wave;                  // one allocation behind the pointers of both sets
   size_t     wave_bytes;
+  cudaStream_t lane[2];
+  cudaEvent_t ev_fork, ev_join[2];
 };
 
 struct bz_lens {
@@ -113,6 +116,7 @@ static thread_local bz_context *gLastContext = nullptr;
 
 static void bz_outline_boxes(const bz_bvh &bvh, std::vector<float> &out);
 static void bz_context_free(bz_context *ctx);
+static int bz_wave_overflowed(bz_context *ctx, bool *out);
 
 static int bz_check_device(int device) {
   int count = 0;
@@ -133,6 +137,11 @@ static void bz_context_free(bz_context *ctx) {
   if(ctx->ev_begin) { cudaEventDestroy(ctx->ev_begin); }
   if(ctx->ev_end) { cudaEventDestroy(ctx->ev_end); }
   if(ctx->ev_tiles) { cudaEventDestroy(ctx->ev_tiles); }
+  if(ctx->ev_fork) { cudaEventDestroy(ctx->ev_fork); }
+  for(int k = 0; k < 2; ++k) {
+    if(ctx->ev_join[k]) { cudaEventDestroy(ctx->ev_join[k]); }
+    if(ctx->lane[k] != nullptr) { cudaStreamDestroy(ctx->lane[k]); }
+  }
   if(ctx->owns_stream && ctx->stream != nullptr) { cudaStreamDestroy(ctx->stream); }
   delete ctx;
 }
@@ -353,15 +362,11 @@ int bz_lens_check(bz_lens *lens) {
   }
   bool overflowed = false;
   for(bz_context *ctx : all) {
-    if(ctx->d_wave == nullptr) { continue; }
     std::lock_guard<std::mutex> hold(ctx->busy);
-    uint32_t flag = 0u;
-    BZ_CUDA(cudaMemcpyAsync(&flag, ctx->wave.counters + 3, sizeof(flag), cudaMemcpyDeviceToHost, ctx->stream));
-    BZ_CUDA(cudaStreamSynchronize(ctx->stream));      // (waits for the work in flight on that stream)
-    if(flag != 0u) {
-      BZ_CUDA(cudaMemsetAsync(ctx->wave.counters + 3, 0, sizeof(flag), ctx->stream));
-      overflowed = true;
-    }
+    bool here = false;
+    int rc = bz_wave_overflowed(ctx, &here);
+    if(rc != BZ_OK) { return rc; }
+    overflowed = overflowed || here;
   }
   if(overflowed) {
     return bz_fail(BZ_ERR_OVERFLOW, "candidate list of the wavefront pipeline overflowed (more than 3 stage-A survivors per ray over a whole chunk): the last frames are incomplete; "
@@ -558,26 +563,48 @@ static int bz_wave_reserve(bz_context *ctx, uint32_t ray_cap) {
   auto round = [](uint64_t bytes) { return (bytes + 255u) / 256u * 256u; };
   uint64_t const sizes[8] = { round((uint64_t)ray_cap * 16u), round((uint64_t)ray_cap * 16u), round((uint64_t)ray_cap * 4u), round(cand_cap * 8u), round(cand_cap * 4u),
                               round(cand_cap * 8u), round(cand_cap * 32u), 256u };
-  uint64_t total = 0u;
-  for(uint64_t size : sizes) { total += size; }
-  if(ctx->d_wave == nullptr || ctx->wave_bytes < total || ctx->wave.ray_cap < ray_cap) {
-    if(ctx->d_wave != nullptr) { BZ_CUDA(cudaFree(ctx->d_wave)); ctx->d_wave = nullptr; ctx->wave_bytes = 0u; }
-    BZ_CUDA(cudaMalloc(&ctx->d_wave, total));
-    BZ_CUDA(cudaMemset(ctx->d_wave, 0, total));
-    ctx->wave_bytes = total;
-    char *at = (char*)ctx->d_wave;
-    ctx->wave.ray_a = (float4*)at; at += sizes[0];
-    ctx->wave.ray_b = (float4*)at; at += sizes[1];
-    ctx->wave.head = (uint32_t*)at; at += sizes[2];
-    ctx->wave.cand = (uint2*)at; at += sizes[3];
-    ctx->wave.cand_next = (uint32_t*)at; at += sizes[4];
-    ctx->wave.cand_key = (unsigned long long*)at; at += sizes[5];
-    ctx->wave.cand_pay = (float4*)at; at += sizes[6];
-    ctx->wave.counters = (uint32_t*)at;
-    ctx->wave.ray_cap = ray_cap;
-    ctx->wave.cand_cap = (uint32_t)std::min<uint64_t>(cand_cap, 0xfffffff0ull);
+  uint64_t one_set = 0u;
+  for(uint64_t size : sizes) { one_set += size; }
+  if(ctx->lane[0] == nullptr) {
+    for(int k = 0; k < 2; ++k) {
+      BZ_CUDA(cudaStreamCreateWithFlags(&ctx->lane[k], cudaStreamNonBlocking));
+      BZ_CUDA(cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming));
+    }
+    BZ_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+  }
+  if(ctx->d_wave == nullptr || ctx->wave_bytes < 2u * one_set || ctx->wave[0].ray_cap < ray_cap) {
+    if(ctx->d_wave != nullptr) {
+      BZ_CUDA(cudaStreamSynchronize(ctx->lane[0]));
+      BZ_CUDA(cudaStreamSynchronize(ctx->lane[1]));
+      BZ_CUDA(cudaFree(ctx->d_wave));
+      ctx->d_wave = nullptr;
+      ctx->wave_bytes = 0u;
+    }
+    BZ_CUDA(cudaMalloc(&ctx->d_wave, 2u * one_set));
+    BZ_CUDA(cudaMemset(ctx->d_wave, 0, 2u * one_set));
+    ctx->wave_bytes = 2u * one_set;
+    for(int k = 0; k < 2; ++k) {
+      char *at = (char*)ctx->d_wave + (size_t)k * one_set;
+      bz_wave &wave = ctx->wave[k];
+      wave.ray_a = (float4*)at; at += sizes[0];
+      wave.ray_b = (float4*)at; at += sizes[1];
+      wave.head = (uint32_t*)at; at += sizes[2];
+      wave.cand = (uint2*)at; at += sizes[3];
+      wave.cand_next = (uint32_t*)at; at += sizes[4];
+      wave.cand_key = (unsigned long long*)at; at += sizes[5];
+      wave.cand_pay = (float4*)at; at += sizes[6];
+      wave.counters = (uint32_t*)at;
+      wave.ray_cap = ray_cap;
+      wave.cand_cap = (uint32_t)std::min<uint64_t>(cand_cap, 0xfffffff0ull);
+    }
   }
   return BZ_OK;
+}
+
+// device memory the wavefront pipeline takes for a job of `slots` ray slots
+static uint64_t bz_wave_bytes(const bz_lens *lens, uint64_t slots) {
+  uint64_t const chunks = std::max<uint64_t>(2u, (slots + lens->wave_chunk - 1u) / lens->wave_chunk);
+  return 2u * ((slots + chunks - 1u) / chunks) * (36u + 52u * BZ_WAVE_CANDS);
 }
 
 static int bz_run_wave(bz_context *ctx, const bz_job &desc) {
@@ -586,21 +613,49 @@ static int bz_run_wave(bz_context *ctx, const bz_job &desc) {
   uint32_t const packets_per_tile = (desc.tile_rays + 31u) / 32u;
   uint32_t const tile_slots = packets_per_tile * 32u;
   uint32_t const tiles = (uint32_t)desc.tile_count;
-  uint32_t const chunk_tiles = std::max<uint32_t>(1u, std::min<uint32_t>(tiles, lens->wave_chunk / tile_slots));
+  // at least two chunks (one per lane), more when a chunk would exceed the configured size
+  uint32_t const chunks = std::max<uint32_t>(tiles >= 2u ? 2u : 1u, (uint32_t)(((uint64_t)tiles * tile_slots + lens->wave_chunk - 1u) / lens->wave_chunk));
+  uint32_t const chunk_tiles = (tiles + chunks - 1u) / chunks;
   int rc = bz_wave_reserve(ctx, chunk_tiles * tile_slots);
   if(rc != BZ_OK) { return rc; }
   uint32_t const levels = std::max<uint32_t>(1u, desc.scene.max_crossings);
-  BZ_CUDA(cudaMemsetAsync(ctx->wave.counters, 0, 3u * sizeof(uint32_t), stream));      // (the kernels leave them zero; a failed launch may not)
-  for(uint32_t first = 0u; first < tiles; first += chunk_tiles) {
-    bz_wave wave = ctx->wave;
+  BZ_CUDA(cudaEventRecord(ctx->ev_fork, stream));
+  for(int k = 0; k < 2; ++k) {
+    BZ_CUDA(cudaStreamWaitEvent(ctx->lane[k], ctx->ev_fork, 0));
+    BZ_CUDA(cudaMemsetAsync(ctx->wave[k].counters, 0, 3u * sizeof(uint32_t), ctx->lane[k]));      // (the kernels leave them zero; a failed launch may not)
+  }
+  uint32_t turn = 0u;
+  for(uint32_t first = 0u; first < tiles; first += chunk_tiles, ++turn) {
+    int const k = (int)(turn & 1u);
+    bz_wave wave = ctx->wave[k];
     wave.first_tile = first;
     wave.tile_count = std::min(chunk_tiles, tiles - first);
     wave.packets_per_tile = packets_per_tile;
     for(uint32_t level = 0u; level < levels; ++level) {
       wave.level = level;
-      if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_wave_pass_fast(lens->tables, desc, wave, lens->sm_count, stream)); }
-      else { BZ_CUDA(bz_launch_wave_pass(lens->tables, desc, wave, lens->sm_count, stream)); }
+      if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_wave_pass_fast(lens->tables, desc, wave, lens->sm_count, ctx->lane[k])); }
+      else { BZ_CUDA(bz_launch_wave_pass(lens->tables, desc, wave, lens->sm_count, ctx->lane[k])); }
       ctx->launches += 3u;
+    }
+  }
+  for(int k = 0; k < 2; ++k) {
+    BZ_CUDA(cudaEventRecord(ctx->ev_join[k], ctx->lane[k]));
+    BZ_CUDA(cudaStreamWaitEvent(stream, ctx->ev_join[k], 0));
+  }
+  return BZ_OK;
+}
+
+// the sticky overflow flags of the context's two candidate lists -> out (synchronises `stream` with the host); cleared when set
+static int bz_wave_overflowed(bz_context *ctx, bool *out) {
+  *out = false;
+  if(ctx->d_wave == nullptr) { return BZ_OK; }
+  uint32_t flags[2] = { 0u, 0u };
+  for(int k = 0; k < 2; ++k) { BZ_CUDA(cudaMemcpyAsync(&flags[k], ctx->wave[k].counters + 3, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream)); }
+  BZ_CUDA(cudaStreamSynchronize(ctx->stream));      // (the lanes were joined into the stream by the call that used them)
+  for(int k = 0; k < 2; ++k) {
+    if(flags[k] != 0u) {
+      BZ_CUDA(cudaMemsetAsync(ctx->wave[k].counters + 3, 0, sizeof(uint32_t), ctx->stream));
+      *out = true;
     }
   }
   return BZ_OK;
@@ -718,7 +773,7 @@ static int bz_run(bz_context *ctx, int job, bz_job &desc) {
     if(job == BZ_JOB_RENDER && lens->pipeline == BZ_PIPELINE_AUTO && lens->mode == BZ_MODE_CULLED && grid != 0) {
       uint64_t const slots = desc.tile_count * (uint64_t)(((desc.tile_rays + 31u) / 32u) * 32u);
       if(slots >= BZ_WAVE_AUTO_RAYS && desc.scene.max_crossings <= BZ_WAVE_AUTO_CROSSINGS) {
-        uint64_t const need = std::min<uint64_t>(slots, lens->wave_chunk) * (36u + 52u * BZ_WAVE_CANDS);
+        uint64_t const need = bz_wave_bytes(lens, slots);
         size_t free_bytes = 0u, total_bytes = 0u;
         wavefront = ctx->wave_bytes >= need || (cudaMemGetInfo(&free_bytes, &total_bytes) == cudaSuccess && need <= free_bytes / 4u);
       }
@@ -969,17 +1024,17 @@ int bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene
   if(rc != BZ_OK) { return rc; }
   BZ_CUDA(cudaMemcpyAsync(h_rgba, d_rgba, bytes, cudaMemcpyDeviceToHost, st));
   bz_stats fresh;
-  uint32_t overflow = 0u;
   if(h_stats != nullptr) { BZ_CUDA(cudaMemcpyAsync(&fresh, d_stats, sizeof(bz_stats), cudaMemcpyDeviceToHost, st)); }
-  if(ctx->d_wave != nullptr) { BZ_CUDA(cudaMemcpyAsync(&overflow, ctx->wave.counters + 3, sizeof(overflow), cudaMemcpyDeviceToHost, st)); }
+  bool overflow = false;
+  rc = bz_wave_overflowed(ctx, &overflow);
+  if(rc != BZ_OK) { return rc; }
   BZ_CUDA(cudaStreamSynchronize(st));
   if(h_stats != nullptr) {
     uint64_t *acc = (uint64_t*)h_stats;
     const uint64_t *add = (const uint64_t*)&fresh;
     for(size_t i = 0u; i < sizeof(bz_stats) / sizeof(uint64_t); ++i) { acc[i] += add[i]; }
   }
-  if(overflow != 0u) {
-    BZ_CUDA(cudaMemsetAsync(ctx->wave.counters + 3, 0, sizeof(overflow), st));
+  if(overflow) {
     return bz_fail(BZ_ERR_OVERFLOW, "candidate list of the wavefront pipeline overflowed: the frame is incomplete; render with bz_lens_set_pipeline(lens, BZ_PIPELINE_PERSISTENT)");
   }
   return BZ_OK;
