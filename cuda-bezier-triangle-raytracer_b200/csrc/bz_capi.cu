@@ -50,7 +50,7 @@ int bz_fail(int code, const std::string &text) {
 
 #define BZ_WAVE_RAYS   (64u << 20)     // default chunk: every kernel boundary costs ~40 us of drained grid, so a frame is one chunk when it fits
 #define BZ_WAVE_CANDS  3u              // candidates reserved per ray slot (the 4K headline frame needs 1.45)
-#define BZ_WAVE_AUTO_RAYS (4ull << 20) // BZ_PIPELINE_AUTO: frames with at least this many ray slots on lens tiles ...
+#define BZ_WAVE_AUTO_RAYS (1ull << 19) // BZ_PIPELINE_AUTO: frames with at least this many ray slots on lens tiles (cfg2: 0.37 vs 0.41 ms; cfg1, below it: 0.16 vs 0.13) ...
 #define BZ_WAVE_AUTO_CROSSINGS 4u      // ... and at most this many crossings (three kernel launches each) take the wavefront pipeline
 
 struct bz_lens;
@@ -607,7 +607,9 @@ static uint64_t bz_wave_bytes(const bz_lens *lens, uint64_t slots) {
   return 2u * ((slots + chunks - 1u) / chunks) * (36u + 52u * BZ_WAVE_CANDS);
 }
 
-static int bz_run_wave(bz_context *ctx, const bz_job &desc) {
+// sky_tiles / sky_count: the tiles beside the lens; bz_sky_kernel is launched on the call's stream AFTER the lanes have their work, so it
+// runs beside the wavefront kernels and fills the SMs they leave idle at their boundaries (nobody else writes those pixels)
+static int bz_run_wave(bz_context *ctx, const bz_job &desc, const uint32_t *sky_tiles, uint32_t sky_count) {
   bz_lens *lens = ctx->lens;
   cudaStream_t const stream = ctx->stream;
   uint32_t const packets_per_tile = (desc.tile_rays + 31u) / 32u;
@@ -638,6 +640,7 @@ static int bz_run_wave(bz_context *ctx, const bz_job &desc) {
       ctx->launches += 3u;
     }
   }
+  if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, sky_tiles, sky_count, stream)); ++ctx->launches; }
   for(int k = 0; k < 2; ++k) {
     BZ_CUDA(cudaEventRecord(ctx->ev_join[k], ctx->lane[k]));
     BZ_CUDA(cudaStreamWaitEvent(stream, ctx->ev_join[k], 0));
@@ -766,7 +769,6 @@ static int bz_run(bz_context *ctx, int job, bz_job &desc) {
   else {
     bz_tables tables = lens->tables;
     if(lens->mode == BZ_MODE_LANES) { tables.packet_count = 0u; }
-    if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, ctx->d_tiles + desc.tile_count, sky_count, stream)); ++ctx->launches; }
     // RENDER: the wavefront pipeline when asked for.  BZ_PIPELINE_AUTO takes it where it measured faster: the
     // parity build, large frames, few crossings -- and only while its ray / candidate lists fit comfortably into free device memory.
     bool wavefront = job == BZ_JOB_RENDER && lens->mode != BZ_MODE_LANES && grid != 0 && lens->pipeline == BZ_PIPELINE_WAVEFRONT;
@@ -779,10 +781,12 @@ static int bz_run(bz_context *ctx, int job, bz_job &desc) {
       }
     }
     if(wavefront) {
-      int rc = bz_run_wave(ctx, desc);
+      int rc = bz_run_wave(ctx, desc, ctx->d_tiles + desc.tile_count, sky_count);
       if(rc != BZ_OK) { return rc; }
+      sky_count = 0u;
     }
-    else if(grid != 0) {
+    if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, ctx->d_tiles + desc.tile_count, sky_count, stream)); ++ctx->launches; }
+    if(!wavefront && grid != 0) {
       if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_warp_trace_fast(job, tables, desc, grid, stream)); }
       else { BZ_CUDA(bz_launch_warp_trace(job, tables, desc, grid, stream)); }
       ++ctx->launches;

@@ -169,7 +169,7 @@ int  bz_lens_patch_count(const bz_lens *lens, uint32_t *out_count);
 /* How bz_render* runs the tiles that can meet the lens (BZ_MODE_CULLED / BZ_MODE_FAST; the results are the same bits):
  *   BZ_PIPELINE_PERSISTENT  one persistent warp-scheduled kernel does walk, stage A, stage B and resolve (csrc/bz_trace.cu)
  *   BZ_PIPELINE_WAVEFRONT   three kernels per surface crossing over global ray / candidate lists (csrc/bz_wave.cu)
- *   BZ_PIPELINE_AUTO        the default: the wavefront kernels for frames of the parity build with at least 4 Mi ray slots on lens tiles and
+ *   BZ_PIPELINE_AUTO        the default: the wavefront kernels for frames of the parity build with at least 2^19 ray slots on lens tiles and
  *                           at most 4 crossings, while their lists (36 bytes per ray slot + 3 x 52 bytes of candidate list per slot; 8.6 GB
  *                           for the 4K x 16 spp headline frame) fit into a quarter of the free device memory; else the persistent kernel
  * The batch entry points (bz_refract_batch, bz_intersect_batch, bz_trace_to_target) always use the persistent kernel. */
