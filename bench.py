@@ -375,23 +375,30 @@ def main_ours(args, name):
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
                 t = json.load(f)
-            if t.get("workload") == name and world == 1:
+            if t.get("workload") == name and world == 1 and t.get("pipeline") == ("wavefront" if launches_per_step > 4 else "persistent"):
                 traffic, traffic_source = t["dram_bytes_read"] + t["dram_bytes_write"], t["source"]
         except (OSError, KeyError, ValueError):
             pass
         flop = FLOP_STAGE_A * own["stage_a"] + FLOP_STAGE_B * own["stage_b"] + FLOP_SNELL * own["snell"]     # rank 0's launch
         k_ms = float(kern.item())
         own_pixels = rows_local * width
+        wavefront = launches_per_step > 4          # (sky + trace + resolve (+ assembly) otherwise)
         hbm_bytes = own_pixels * (BYTES_PER_PIXEL_OUT + BYTES_PER_PIXEL_ACCUM)
+        if wavefront:
+            # the lists of the wavefront pipeline: per evaluated candidate 8 B entry + 32 B ray read, 8 B key + 32 B hit record written;
+            # per traced ray slot and crossing 36 B ray state + chain head written by the walk, 36 B read and 32 B rewritten by the resolve
+            hbm_bytes += 80 * own["stage_b"] + 104 * (32 * own["packet_walks"] + own["lane_walk_calls"])
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         achieved_tf = flop / (k_ms * 1e-3) / 1e12
         sm_max = (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz", 1965.0)
         nominal_tf = lens.info()["sm_count"] * 128 * 2 * sm_max * 1e6 / 1e12
         roofline = {
-            "bound": "fp32_alu", "kernel": "bz_warp_trace_kernel<RENDER> (kernel_ms = the trace kernels + bz_sky_kernel of one step, CUDA events on the launching stream)",
+            "bound": "fp32_alu",
+            "kernel": ("bz_wave_walk_kernel + bz_wave_eval_kernel + bz_wave_resolve_kernel (wavefront pipeline)" if wavefront else "bz_warp_trace_kernel<RENDER> (persistent kernel)")
+                      + "; kernel_ms = the trace kernels + bz_sky_kernel of one step, CUDA events on the launching stream",
             "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
             "peak_nominal": nominal_tf, "frac_of_nominal": achieved_tf / nominal_tf,
-            "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_source,
+            "traffic": traffic, "traffic_unit": "DRAM bytes of the trace kernels of one step (ncu, summed over their launches)", "traffic_source": traffic_source,
             "frac_of_no_fma_ceiling": achieved_tf / (peak_tf / 2.0),
             "no_fma_note": "the parity build has no FMA contraction (bit-exact with the reference's x86 build): one flop per lane and instruction, half the probe's peak",
             "peak_source": "FMA probe kernel in this process (16 independent chains per thread, 2 flop/lane/instr); peak_nominal = SMs x 128 lanes x 2 x %.0f MHz" % sm_max,

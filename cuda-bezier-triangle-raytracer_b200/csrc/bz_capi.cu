@@ -626,12 +626,13 @@ static int bz_run_wave(bz_context *ctx, const bz_job &desc, const uint32_t *sky_
     BZ_CUDA(cudaStreamWaitEvent(ctx->lane[k], ctx->ev_fork, 0));
     BZ_CUDA(cudaMemsetAsync(ctx->wave[k].counters, 0, 3u * sizeof(uint32_t), ctx->lane[k]));      // (the kernels leave them zero; a failed launch may not)
   }
-  uint32_t turn = 0u;
-  for(uint32_t first = 0u; first < tiles; first += chunk_tiles, ++turn) {
+  // chunk c takes the tiles c, c + chunks, c + 2 chunks, ... of the hand-out order (heaviest first), so all chunks weigh the same
+  for(uint32_t turn = 0u; turn < chunks && turn < tiles; ++turn) {
     int const k = (int)(turn & 1u);
     bz_wave wave = ctx->wave[k];
-    wave.first_tile = first;
-    wave.tile_count = std::min(chunk_tiles, tiles - first);
+    wave.first_tile = turn;
+    wave.tile_stride = chunks;
+    wave.tile_count = (tiles - turn + chunks - 1u) / chunks;
     wave.packets_per_tile = packets_per_tile;
     for(uint32_t level = 0u; level < levels; ++level) {
       wave.level = level;

@@ -118,7 +118,8 @@ struct bz_wave {
   uint32_t *counters;       // [0] next packet of the walk  [1] candidates of this pass  [2] next batch of the evaluation
                             // [3] sticky: the candidate buffer overflowed (the frame is incomplete, the next call reports it)
   uint32_t  ray_cap, cand_cap;
-  uint32_t  first_tile;     // chunk = tiles [first_tile, first_tile + tile_count) of the job's tile order
+  uint32_t  first_tile;     // chunk = tiles first_tile + i * tile_stride, i < tile_count, of the job's tile order (heaviest first:
+  uint32_t  tile_stride;    // interleaved chunks carry equal shares of the heavy tiles)
   uint32_t  tile_count;
   uint32_t  packets_per_tile;
   uint32_t  level;          // 0: the walk kernel generates the primary rays

@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(32 * BZV_WALK_WARPS, BZV_WALK_CTAS) bz_wave_wa
     bzv3 s = bz_v(0.0f, 0.0f, 0.0f), d = s;
     bool live = false;
     if(W.level == 0u) {
-      const uint32_t tile = bzv_tile_of(J, W.first_tile + in_chunk);
+      const uint32_t tile = bzv_tile_of(J, W.first_tile + in_chunk * W.tile_stride);
       const uint32_t at = in_tile * 32u + lane;
       const uint32_t inside = bzw_div(at, J.div_spp), sample = at - inside * spp;      // pixel of the tile in Morton order, sample of the pixel
       const uint32_t tile_y = tile / J.tiles_x, tile_x = tile - tile_y * J.tiles_x;
