@@ -375,8 +375,9 @@ def main_ours(args, name):
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
                 t = json.load(f)
-            if t.get("workload") == name and world == 1 and t.get("pipeline") == ("wavefront" if launches_per_step > 4 else "persistent"):
-                traffic, traffic_source = t["dram_bytes_read"] + t["dram_bytes_write"], t["source"]
+            for entry in (t if isinstance(t, list) else [t]):
+                if entry.get("workload") == name and world == 1 and args.mode == "exact" and entry.get("pipeline") == ("wavefront" if launches_per_step > 4 else "persistent"):
+                    traffic, traffic_source = entry["dram_bytes_read"] + entry["dram_bytes_write"], entry["source"]
         except (OSError, KeyError, ValueError):
             pass
         flop = FLOP_STAGE_A * own["stage_a"] + FLOP_STAGE_B * own["stage_b"] + FLOP_SNELL * own["snell"]     # rank 0's launch

@@ -36,7 +36,7 @@ namespace BZ_NS {
 
 #define BZV_WALK_WARPS   8
 #ifndef BZV_WALK_CTAS
-#define BZV_WALK_CTAS    3       // resident CTAs per SM the walk kernel is compiled for (register budget)
+#define BZV_WALK_CTAS    4       // resident CTAs per SM the walk kernel is compiled for (64 registers, 16 B of spills; 3 CTAs at 72 registers measured 0.7 % slower)
 #endif
 #ifndef BZV_EVAL_WARPS
 #define BZV_EVAL_WARPS   4
