@@ -102,6 +102,7 @@ struct bz_lens {
   uint32_t   mode;
   uint32_t   pipeline;                // BZ_PIPELINE_*
   uint32_t   wave_chunk;              // ray slots per chunk of the wavefront pipeline
+  uint32_t   wave_unit;               // packets per hand-out unit of the walk kernel
   bz_tables  tables;
   float4    *d_cull, *d_newton, *d_leaf, *d_pairs, *d_nodes, *d_packet;
   uint32_t   bvh_depth;
@@ -276,6 +277,7 @@ int bz_lens_create(const bz_patch *h_patches, uint32_t patch_count, float refrac
   lens->device = device;
   lens->mode = BZ_MODE_CULLED;
   lens->wave_chunk = BZ_WAVE_RAYS;
+  lens->wave_unit = 8u;                   // (one packet per warp of a walk CTA)
   lens->bvh_depth = bvh.depth;
   bz_outline_boxes(bvh, lens->outline);
   cudaDeviceProp prop;
@@ -634,6 +636,13 @@ static int bz_run_wave(bz_context *ctx, const bz_job &desc, const uint32_t *sky_
     wave.tile_stride = chunks;
     wave.tile_count = (tiles - turn + chunks - 1u) / chunks;
     wave.packets_per_tile = packets_per_tile;
+    wave.unit_packets = std::min(packets_per_tile, lens->wave_unit);
+    wave.units_per_tile = (packets_per_tile + wave.unit_packets - 1u) / wave.unit_packets;
+    // the heaviest sixteenth of the chunk's tiles, and at least eight tiles per SM, go out in parts (measured, cfg4: the walk launches of the
+    // two ranks of eight that own the poles of the body 2.30 -> 2.13 ms per frame share, the whole frame on one GPU +0.3 %; all tiles in
+    // parts: 2.12 ms and +3.4 % -- the parts of a tile no longer meet in one SM's L1)
+    wave.split_tiles = std::min(wave.tile_count, std::max((wave.tile_count + 15u) / 16u, 8u * (uint32_t)lens->sm_count));
+    wave.unit_count = wave.split_tiles * wave.units_per_tile + (wave.tile_count - wave.split_tiles);
     for(uint32_t level = 0u; level < levels; ++level) {
       wave.level = level;
       if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_wave_pass_fast(lens->tables, desc, wave, lens->sm_count, ctx->lane[k])); }

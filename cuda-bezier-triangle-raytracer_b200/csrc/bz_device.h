@@ -122,6 +122,10 @@ struct bz_wave {
   uint32_t  tile_stride;    // interleaved chunks carry equal shares of the heavy tiles)
   uint32_t  tile_count;
   uint32_t  packets_per_tile;
+  uint32_t  split_tiles;    // the walk kernel hands the first split_tiles tiles of the chunk to its CTAs in parts of unit_packets
+  uint32_t  unit_packets;   // consecutive packets (units_per_tile = ceil(packets_per_tile / unit_packets) parts per tile), the
+  uint32_t  units_per_tile; // other tiles whole; unit_count = split_tiles * units_per_tile + (tile_count - split_tiles)
+  uint32_t  unit_count;
   uint32_t  level;          // 0: the walk kernel generates the primary rays
 };
 

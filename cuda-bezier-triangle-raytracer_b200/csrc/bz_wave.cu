@@ -106,20 +106,30 @@ __device__ __forceinline__ void bzv_flush(bzv_walk_pool &P, const bz_wave &W, ui
 // is the first one past the end of the tile fetches the next tile and takes its first packet; the others wait for it.
 __device__ __forceinline__ unsigned long long bzv_fetch_tile(const bz_wave &W) {
   const uint32_t next = atomicAdd(W.counters, 1u);
-  return (unsigned long long)(next < W.tile_count ? next : BZ_END) << 32;
+  return (unsigned long long)(next < W.unit_count ? next : BZ_END) << 32;
+}
+
+// The unit of the hand-out: the first W.split_tiles tiles of the chunk (the heaviest: the fan of thin patches around a pole of the body
+// costs a hundred times an ordinary tile) go out in parts of W.unit_packets consecutive packets, so that several SMs share them instead
+// of one CTA being the tail of the launch; the others go out whole.  Units [0, split_tiles * units_per_tile) are the parts.
+__device__ __forceinline__ uint32_t bzv_unit_packets(const bz_wave &W, uint32_t unit) {
+  if(unit >= W.split_tiles * W.units_per_tile) { return W.packets_per_tile; }
+  return min(W.unit_packets, W.packets_per_tile - (unit % W.units_per_tile) * W.unit_packets);
 }
 
 __device__ __forceinline__ unsigned long long bzv_take_packet(unsigned long long *cta_work, const bz_wave &W) {
   for(;;) {
     const unsigned long long w = atomicAdd(cta_work, 1ull);
-    const uint32_t tile = (uint32_t)(w >> 32), at = (uint32_t)w;
-    if(tile == BZ_END || at < W.packets_per_tile) { return w; }
-    if(at == W.packets_per_tile) {
+    const uint32_t unit = (uint32_t)(w >> 32), at = (uint32_t)w;
+    if(unit == BZ_END) { return w; }
+    const uint32_t limit = bzv_unit_packets(W, unit);
+    if(at < limit) { return w; }
+    if(at == limit) {
       const unsigned long long fresh = bzv_fetch_tile(W);
       atomicExch(cta_work, fresh | 1ull);
       return fresh;
     }
-    while((uint32_t)(*(volatile unsigned long long*)cta_work >> 32) == tile) { __nanosleep(64); }
+    while((uint32_t)(*(volatile unsigned long long*)cta_work >> 32) == unit) { __nanosleep(64); }
   }
 }
 
@@ -142,8 +152,14 @@ __global__ void __launch_bounds__(32 * BZV_WALK_WARPS, BZV_WALK_CTAS) bz_wave_wa
     unsigned long long work = 0ull;
     if(lane == 0u) { work = bzv_take_packet(&cta_work, W); }
     work = __shfl_sync(0xffffffffu, work, 0);
-    const uint32_t in_chunk = (uint32_t)(work >> 32), in_tile = (uint32_t)work;
-    if(in_chunk == BZ_END) { break; }
+    const uint32_t unit = (uint32_t)(work >> 32);
+    if(unit == BZ_END) { break; }
+    uint32_t in_chunk, in_tile = (uint32_t)work;      // tile of the chunk, packet of the tile
+    if(unit >= W.split_tiles * W.units_per_tile) { in_chunk = unit - W.split_tiles * (W.units_per_tile - 1u); }
+    else {
+      in_chunk = unit / W.units_per_tile;
+      in_tile += (unit - in_chunk * W.units_per_tile) * W.unit_packets;
+    }
     const uint32_t packet = in_chunk * W.packets_per_tile + in_tile;
     const uint32_t slot_base = packet * 32u, ray_slot = slot_base + lane;
     // ---- the packet's rays: generated (first crossing) or reloaded ----
