@@ -143,6 +143,7 @@ SIGNATURES = {
     "bz_generate_rays": (_int, [C.POINTER(Camera), _u32, _u32, _vp, _vp, _vp]),
     "bz_render": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _vp, _vp, _vp]),
     "bz_render_host": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _vp, C.POINTER(Stats)]),
+    "bz_render_static": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _vp, _vp, _vp]),
     "bz_striped_rows": (_u32, [_u32, _u32, _u32, _u32]),
     "bz_render_striped": (_int, [_vp, C.POINTER(Camera), C.POINTER(Scene), _u32, _u32, _u32, _vp, _vp, _vp]),
     "bz_assemble_stripes": (_int, [_vp, _u32, _u32, _u32, _u32, _u32, _vp, _vp]),
@@ -543,6 +544,11 @@ class BezierLens:
     def render_device(self, camera, scene, rgba, row0=0, row1=None, stats=None, stream=None):
         row1 = camera.height if row1 is None else row1
         _check(self.lib.bz_render(self.h, C.byref(camera), C.byref(scene), row0, row1, _ptr(rgba), _ptr(stats), _stream_handle(stream)))
+
+    def render_static_device(self, camera, scene, rgba, row0=0, row1=None, stats=None, stream=None):
+        """bz_render_static: the render without any allocation (static device scratch, at most STATIC_MAX_PIXELS pixels per call)"""
+        row1 = camera.height if row1 is None else row1
+        _check(self.lib.bz_render_static(self.h, C.byref(camera), C.byref(scene), row0, row1, _ptr(rgba), _ptr(stats), _stream_handle(stream)))
 
     def render_striped_device(self, camera, scene, stripe_rows, rank, ranks, rgba, stats=None, stream=None):
         _check(self.lib.bz_render_striped(self.h, C.byref(camera), C.byref(scene), stripe_rows, rank, ranks, _ptr(rgba), _ptr(stats),

@@ -988,6 +988,102 @@ int bz_render(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uin
   return bz_render_common(ctx, camera, scene, row0, row1 - row0, 0u, 0u, 1u, d_rgba, d_stats);
 }
 
+// ---- bz_render_static: bz_render for callers that may not allocate (no counterpart in the reference).
+// The scratch of the render -- the work counter of the persistent kernel and one u32 accumulator per pixel -- lives in a
+// file-scope device array instead of the context's cudaMalloc'ed buffers; nothing on this path allocates or frees.  Every GPU that loads the
+// library holds the array (8 MiB + 256 B) until exit; all calls share it, so calls that overlap on one GPU race.
+static __device__ __align__(256) unsigned char bz_static_scratch[256u + (size_t)BZ_STATIC_MAX_PIXELS * sizeof(uint32_t)];
+
+// the array's device address on `device` (which is current); asked once per device -- in host code the array's NAME is a host-side
+// stand-in, not a device address
+static int bz_static_scratch_address(int device, unsigned char **out) {
+  static std::mutex guard;
+  static unsigned char *address[64] = {};
+  if(device < 0 || device >= 64) { return bz_fail(BZ_ERR_INVALID, "device index out of range"); }
+  std::lock_guard<std::mutex> hold(guard);
+  if(address[device] == nullptr) {
+    void *p = nullptr;
+    cudaError_t const e = cudaGetSymbolAddress(&p, bz_static_scratch);
+    if(e != cudaSuccess || p == nullptr) { return bz_fail(BZ_ERR_CUDA, std::string("cudaGetSymbolAddress(bz_static_scratch): ") + cudaGetErrorString(e)); }
+    address[device] = (unsigned char*)p;
+  }
+  *out = address[device];
+  return BZ_OK;
+}
+
+int bz_render_static(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
+                     uint8_t *d_rgba, bz_stats *d_stats, void *stream) {
+  if(lens == nullptr || camera == nullptr || scene == nullptr) { return bz_fail(BZ_ERR_INVALID, "null argument"); }
+  if(row1 < row0 || row1 > camera->height) { return bz_fail(BZ_ERR_INVALID, "bad rows"); }
+  if(camera->width == 0u || camera->height == 0u || camera->strata == 0u) { return bz_fail(BZ_ERR_INVALID, "empty camera"); }
+  uint32_t const rows = row1 - row0;
+  if(rows == 0u) { return BZ_OK; }
+  if(d_rgba == nullptr) { return bz_fail(BZ_ERR_INVALID, "d_rgba is null"); }
+  uint64_t const pixels = (uint64_t)rows * camera->width;
+  if(pixels > BZ_STATIC_MAX_PIXELS) {
+    return bz_fail(BZ_ERR_INVALID, "bz_render_static: " + std::to_string(pixels) + " pixels exceed the static scratch of " + std::to_string(BZ_STATIC_MAX_PIXELS)
+                                   + " (BZ_STATIC_MAX_PIXELS); render the frame in row bands or use bz_render");
+  }
+  if(camera->strata > 128u) { return bz_fail(BZ_ERR_INVALID, "more than 128 x 128 samples per pixel"); }
+  cudaStream_t const st = (cudaStream_t)stream;
+  BZ_CUDA(cudaSetDevice(lens->device));
+  unsigned char *scratch = nullptr;
+  int rc = bz_static_scratch_address(lens->device, &scratch);
+  if(rc != BZ_OK) { return rc; }
+  unsigned long long *counter = (unsigned long long*)scratch;
+  uint32_t *accum = (uint32_t*)(scratch + 256u);
+  // the array keeps the last call's contents: the counter and the accumulators of this band start at zero
+  BZ_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st));
+  BZ_CUDA(cudaMemsetAsync(accum, 0, (size_t)pixels * sizeof(uint32_t), st));
+  uint32_t const spp = camera->strata * camera->strata;
+  bz_job desc;
+  std::memset(&desc, 0, sizeof(desc));
+  desc.camera = *camera;
+  desc.scene = *scene;
+  desc.row0 = row0;
+  desc.rows = rows;
+  desc.stripe_ranks = 1u;
+  desc.accum = accum;
+  desc.next_ray = counter;
+  desc.one = 1.0f;
+  desc.ray_count = pixels * spp;
+  desc.stats = (unsigned long long*)d_stats;
+  if(lens->mode == BZ_MODE_BRUTE) {
+    uint64_t const threads = (uint64_t)bz_trace_threads();
+    int const grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * 2u, (desc.ray_count + threads - 1u) / threads);
+    BZ_CUDA(bz_launch_trace(BZ_JOB_RENDER, true, lens->tables, desc, grid, st));
+  }
+  else {
+    // the tiles of bz_run, all of them traced by the persistent kernel: no tile plan (its list is a per-frame upload into an allocated
+    // buffer), so the rays beside the lens go through the root test of the walk instead of bz_sky_kernel -- same pixels, more time
+    uint32_t side = 32u;
+    while(side > 2u && (uint64_t)side * side * spp > 1536u) { side /= 2u; }
+    auto tiles_of = [&](uint32_t s) { return (uint64_t)((camera->width + s - 1u) / s) * ((rows + s - 1u) / s); };
+    while(side > 4u && (uint64_t)side * side * spp >= 1024u && tiles_of(side) < 16ull * (uint64_t)lens->sm_count) { side /= 2u; }
+    auto reciprocal = [](uint32_t d, uint32_t out[2]) { out[0] = (d <= 1u) ? 0u : (uint32_t)(((1ull << 32) + d - 1u) / d); out[1] = (d == 1u) ? 1u : 0u; };
+    reciprocal(spp, desc.div_spp);
+    reciprocal(camera->strata, desc.div_strata);
+    reciprocal(0u, desc.div_stripe);
+    desc.two_over_w = 2.0f / (float)camera->width;
+    desc.two_over_h = 2.0f / (float)camera->height;
+    desc.tile_side = side;
+    desc.tile_rays = side * side * spp;
+    desc.tiles_x = (camera->width + side - 1u) / side;
+    desc.tiles_y = (rows + side - 1u) / side;
+    desc.tile_count = (uint64_t)desc.tiles_x * desc.tiles_y;
+    int perSm = 0, raysPerCta = 0;
+    if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_warp_trace_occupancy_fast(&perSm, &raysPerCta)); }
+    else { BZ_CUDA(bz_warp_trace_occupancy(&perSm, &raysPerCta)); }
+    int const grid = (int)std::min<uint64_t>((uint64_t)lens->sm_count * (uint64_t)std::max(perSm, 1), desc.tile_count);
+    bz_tables tables = lens->tables;
+    if(lens->mode == BZ_MODE_LANES) { tables.packet_count = 0u; }
+    if(lens->mode == BZ_MODE_FAST) { BZ_CUDA(bz_launch_warp_trace_fast(BZ_JOB_RENDER, tables, desc, grid, st)); }
+    else { BZ_CUDA(bz_launch_warp_trace(BZ_JOB_RENDER, tables, desc, grid, st)); }
+  }
+  BZ_CUDA(bz_launch_resolve(accum, d_rgba, (size_t)pixels, spp, st));
+  return BZ_OK;
+}
+
 uint32_t bz_striped_rows(uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t ranks) {
   if(stripe_rows == 0u || ranks == 0u || rank >= ranks) { return 0u; }
   uint32_t rows = 0u;

@@ -227,6 +227,20 @@ int  bz_render(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, ui
 int  bz_render_host(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
                     uint8_t *h_rgba, bz_stats *h_stats);
 
+/* bz_render without any allocation.  No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same pixels and
+ * same d_stats counts of stage A / B / Snell work as bz_render on the same lens (any mode; the pipeline setting is ignored: always the
+ * persistent kernel, and no tile plan, so rays beside the lens are traced instead of going to the sky kernel -- slower on frames that are
+ * mostly background, and node_visits / packet counters are larger).  The render's scratch (work counter + one u32 accumulator per pixel)
+ * is a static device array of 256 + 4 * BZ_STATIC_MAX_PIXELS bytes (8 MiB: a 1920 x 1080 band) that every GPU loading the library holds
+ * until exit; (row1 - row0) * width beyond BZ_STATIC_MAX_PIXELS is BZ_ERR_INVALID (render in row bands, or use bz_render).  The call issues
+ * memsets and kernels on `stream` and calls no cudaMalloc / cudaFree; it creates no context for the stream and leaves bz_last_kernel_ms /
+ * bz_last_kernel_launches untouched.  ALL calls, from any lens, thread or stream, share the one array per GPU: calls that overlap on a
+ * GPU race (serialise them on one stream, or with events); the array keeps the last call's contents and each call clears what it uses. */
+#define BZ_STATIC_MAX_PIXELS 2097152u
+int  bz_render_static(bz_lens *lens, const bz_camera *camera, const bz_scene *scene, uint32_t row0, uint32_t row1,
+                      uint8_t *d_rgba, bz_stats *d_stats, void *stream);
+
 /* Row bands for N GPUs (north_star subsystem 4): the image is cut into stripes of `stripe_rows` rows
  * dealt round-robin to `ranks` ranks; rank r renders stripes r, r+ranks, ... into a compact local
  * buffer (its rows in image order).  bz_striped_rows gives that buffer's row count. */
