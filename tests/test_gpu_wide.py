@@ -233,6 +233,24 @@ def test_pipelines_give_the_same_frame(bz, name):
         lens.check()
 
 
+@pytest.mark.parametrize("strata,width,height", [(3, 333, 217), (5, 150, 101), (7, 64, 40), (1, 1001, 600)])
+def test_wavefront_ragged_tiles_and_parts(bz, strata, width, height):
+    """samples per pixel that make the packets of a tile ragged (9 spp: 18 packets = parts of 8 + 8 + 2; 25 spp: 13 packets, the last
+    half full; 49 spp: one pixel per ... tile sides 4 and 2) and frame sizes that cut the border tiles: the walk kernel's hand-out in
+    parts of tiles gives the persistent kernel's frame and counts"""
+    from bezier_b200 import workloads
+    spec, mesh, cam_kw, scene_kw = workloads.setup("cfg2_ellipsoid64x32_1080p", bz.Mesh)
+    lens = bz.BezierLens(spec["ri"], bz.BezierMesh(mesh))
+    cam, scene = bz.make_camera(width, height, **dict(cam_kw, strata=strata)), bz.make_scene(**scene_kw)
+    want, want_stats = lens.set_pipeline(bz.PIPELINE_PERSISTENT).render(cam, scene)
+    assert want_stats.entered > 1000
+    for chunk in (1 << 26, 50000, 2000):
+        rgba, stats = lens.set_pipeline(bz.PIPELINE_WAVEFRONT).set_wave_chunk(chunk).render(cam, scene)
+        assert np.array_equal(rgba, want), "chunk %d: %d pixels differ" % (chunk, int((rgba != want).any(-1).sum()))
+        assert stats.as_dict() == want_stats.as_dict(), chunk
+        lens.check()
+
+
 def test_one_lens_many_streams_and_threads(bz, oracle_built):
     """BezierLens::refract is const and re-entrant (reference/bezierLens.h:27): ONE lens handle serves two cameras rendered
     concurrently on two streams (both pipelines) while host threads refract and render through the *_host calls; every result
