@@ -48,6 +48,9 @@ int bz_fail(int code, const std::string &text) {
 #define BZ_CUDA(call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) { \
   return bz_fail(BZ_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while(0)
 
+#ifndef BZ_WAVE_LANES
+#define BZ_WAVE_LANES 2       // buffer sets / internal streams the chunks of a frame alternate between
+#endif
 #define BZ_WAVE_RAYS   (64u << 20)     // default chunk: every kernel boundary costs ~40 us of drained grid, so a frame is one chunk when it fits
 #define BZ_WAVE_CANDS  3u              // candidates reserved per ray slot (the 4K headline frame needs 1.45)
 #define BZ_WAVE_AUTO_RAYS (1ull << 19) // BZ_PIPELINE_AUTO: frames with at least this many ray slots on lens tiles (cfg2: 0.37 vs 0.41 ms; cfg1, below it: 0.16 vs 0.13) ...
@@ -89,11 +92,11 @@ struct bz_context {
   uint32_t   launches;                // kernels of the most recent call
   // RENDER, wavefront pipeline (csrc/bz_wave.cu): two sets of ray slots + candidate list, each with a stream of its own -- the chunks of a
   // frame alternate between them, so that one chunk's kernels fill the drained grid at the other's kernel boundaries
-  bz_wave    wave[2];
+  bz_wave    wave[BZ_WAVE_LANES];
   void      *d_wave;                  // one allocation behind the pointers of both sets
   size_t     wave_bytes;
-  cudaStream_t lane[2];
-  cudaEvent_t ev_fork, ev_join[2];
+  cudaStream_t lane[BZ_WAVE_LANES];
+  cudaEvent_t ev_fork, ev_join[BZ_WAVE_LANES];
 };
 
 struct bz_lens {
@@ -139,7 +142,7 @@ static void bz_context_free(bz_context *ctx) {
   if(ctx->ev_end) { cudaEventDestroy(ctx->ev_end); }
   if(ctx->ev_tiles) { cudaEventDestroy(ctx->ev_tiles); }
   if(ctx->ev_fork) { cudaEventDestroy(ctx->ev_fork); }
-  for(int k = 0; k < 2; ++k) {
+  for(int k = 0; k < BZ_WAVE_LANES; ++k) {
     if(ctx->ev_join[k]) { cudaEventDestroy(ctx->ev_join[k]); }
     if(ctx->lane[k] != nullptr) { cudaStreamDestroy(ctx->lane[k]); }
   }
@@ -568,24 +571,23 @@ static int bz_wave_reserve(bz_context *ctx, uint32_t ray_cap) {
   uint64_t one_set = 0u;
   for(uint64_t size : sizes) { one_set += size; }
   if(ctx->lane[0] == nullptr) {
-    for(int k = 0; k < 2; ++k) {
+    for(int k = 0; k < BZ_WAVE_LANES; ++k) {
       BZ_CUDA(cudaStreamCreateWithFlags(&ctx->lane[k], cudaStreamNonBlocking));
       BZ_CUDA(cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming));
     }
     BZ_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
   }
-  if(ctx->d_wave == nullptr || ctx->wave_bytes < 2u * one_set || ctx->wave[0].ray_cap < ray_cap) {
+  if(ctx->d_wave == nullptr || ctx->wave_bytes < (uint64_t)BZ_WAVE_LANES * one_set || ctx->wave[0].ray_cap < ray_cap) {
     if(ctx->d_wave != nullptr) {
-      BZ_CUDA(cudaStreamSynchronize(ctx->lane[0]));
-      BZ_CUDA(cudaStreamSynchronize(ctx->lane[1]));
+      for(int k = 0; k < BZ_WAVE_LANES; ++k) { BZ_CUDA(cudaStreamSynchronize(ctx->lane[k])); }
       BZ_CUDA(cudaFree(ctx->d_wave));
       ctx->d_wave = nullptr;
       ctx->wave_bytes = 0u;
     }
-    BZ_CUDA(cudaMalloc(&ctx->d_wave, 2u * one_set));
-    BZ_CUDA(cudaMemset(ctx->d_wave, 0, 2u * one_set));
-    ctx->wave_bytes = 2u * one_set;
-    for(int k = 0; k < 2; ++k) {
+    BZ_CUDA(cudaMalloc(&ctx->d_wave, (uint64_t)BZ_WAVE_LANES * one_set));
+    BZ_CUDA(cudaMemset(ctx->d_wave, 0, (uint64_t)BZ_WAVE_LANES * one_set));
+    ctx->wave_bytes = (uint64_t)BZ_WAVE_LANES * one_set;
+    for(int k = 0; k < BZ_WAVE_LANES; ++k) {
       char *at = (char*)ctx->d_wave + (size_t)k * one_set;
       bz_wave &wave = ctx->wave[k];
       wave.ray_a = (float4*)at; at += sizes[0];
@@ -605,8 +607,8 @@ static int bz_wave_reserve(bz_context *ctx, uint32_t ray_cap) {
 
 // device memory the wavefront pipeline takes for a job of `slots` ray slots
 static uint64_t bz_wave_bytes(const bz_lens *lens, uint64_t slots) {
-  uint64_t const chunks = std::max<uint64_t>(2u, (slots + lens->wave_chunk - 1u) / lens->wave_chunk);
-  return 2u * ((slots + chunks - 1u) / chunks) * (36u + 52u * BZ_WAVE_CANDS);
+  uint64_t const chunks = std::max<uint64_t>(BZ_WAVE_LANES, (slots + lens->wave_chunk - 1u) / lens->wave_chunk);
+  return (uint64_t)BZ_WAVE_LANES * ((slots + chunks - 1u) / chunks) * (36u + 52u * BZ_WAVE_CANDS);
 }
 
 // sky_tiles / sky_count: the tiles beside the lens; bz_sky_kernel is launched on the call's stream AFTER the lanes have their work, so it
@@ -618,19 +620,19 @@ static int bz_run_wave(bz_context *ctx, const bz_job &desc, const uint32_t *sky_
   uint32_t const tile_slots = packets_per_tile * 32u;
   uint32_t const tiles = (uint32_t)desc.tile_count;
   // at least two chunks (one per lane), more when a chunk would exceed the configured size
-  uint32_t const chunks = std::max<uint32_t>(tiles >= 2u ? 2u : 1u, (uint32_t)(((uint64_t)tiles * tile_slots + lens->wave_chunk - 1u) / lens->wave_chunk));
+  uint32_t const chunks = std::max<uint32_t>(std::min<uint32_t>(tiles, BZ_WAVE_LANES), (uint32_t)(((uint64_t)tiles * tile_slots + lens->wave_chunk - 1u) / lens->wave_chunk));
   uint32_t const chunk_tiles = (tiles + chunks - 1u) / chunks;
   int rc = bz_wave_reserve(ctx, chunk_tiles * tile_slots);
   if(rc != BZ_OK) { return rc; }
   uint32_t const levels = std::max<uint32_t>(1u, desc.scene.max_crossings);
   BZ_CUDA(cudaEventRecord(ctx->ev_fork, stream));
-  for(int k = 0; k < 2; ++k) {
+  for(int k = 0; k < BZ_WAVE_LANES; ++k) {
     BZ_CUDA(cudaStreamWaitEvent(ctx->lane[k], ctx->ev_fork, 0));
     BZ_CUDA(cudaMemsetAsync(ctx->wave[k].counters, 0, 3u * sizeof(uint32_t), ctx->lane[k]));      // (the kernels leave them zero; a failed launch may not)
   }
   // chunk c takes the tiles c, c + chunks, c + 2 chunks, ... of the hand-out order (heaviest first), so all chunks weigh the same
   for(uint32_t turn = 0u; turn < chunks && turn < tiles; ++turn) {
-    int const k = (int)(turn & 1u);
+    int const k = (int)(turn % BZ_WAVE_LANES);
     bz_wave wave = ctx->wave[k];
     wave.first_tile = turn;
     wave.tile_stride = chunks;
@@ -651,7 +653,7 @@ static int bz_run_wave(bz_context *ctx, const bz_job &desc, const uint32_t *sky_
     }
   }
   if(sky_count != 0u) { BZ_CUDA(bz_launch_sky(desc, sky_tiles, sky_count, stream)); ++ctx->launches; }
-  for(int k = 0; k < 2; ++k) {
+  for(int k = 0; k < BZ_WAVE_LANES; ++k) {
     BZ_CUDA(cudaEventRecord(ctx->ev_join[k], ctx->lane[k]));
     BZ_CUDA(cudaStreamWaitEvent(stream, ctx->ev_join[k], 0));
   }
@@ -662,10 +664,10 @@ static int bz_run_wave(bz_context *ctx, const bz_job &desc, const uint32_t *sky_
 static int bz_wave_overflowed(bz_context *ctx, bool *out) {
   *out = false;
   if(ctx->d_wave == nullptr) { return BZ_OK; }
-  uint32_t flags[2] = { 0u, 0u };
-  for(int k = 0; k < 2; ++k) { BZ_CUDA(cudaMemcpyAsync(&flags[k], ctx->wave[k].counters + 3, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream)); }
+  uint32_t flags[BZ_WAVE_LANES] = {};
+  for(int k = 0; k < BZ_WAVE_LANES; ++k) { BZ_CUDA(cudaMemcpyAsync(&flags[k], ctx->wave[k].counters + 3, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream)); }
   BZ_CUDA(cudaStreamSynchronize(ctx->stream));      // (the lanes were joined into the stream by the call that used them)
-  for(int k = 0; k < 2; ++k) {
+  for(int k = 0; k < BZ_WAVE_LANES; ++k) {
     if(flags[k] != 0u) {
       BZ_CUDA(cudaMemsetAsync(ctx->wave[k].counters + 3, 0, sizeof(uint32_t), ctx->stream));
       *out = true;
