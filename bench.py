@@ -6,8 +6,8 @@
 
 One step = one whole frame of the workload (default: cfg4, makeEllipsoid(181,91,(1,4,2)) -> 98 826 patches,
 3840x2160, 16 rays/pixel = 132 710 400 primary rays), image rows dealt to the N ranks in round-robin stripes
-of 8 rows, tables replicated, the rendered stripes gathered on rank 0 by bz_gather_rows (C ABI: NCCL send / recv
-over NVLink, assembly on the device) when N > 1 (strong scaling: the frame is fixed).
+of 8 rows, tables replicated, the rendered stripes gathered on rank 0 by bz_gather_rows (C ABI: every rank stores its
+rows into the root's IPC-mapped frame over NVLink; --gather nccl: send / recv + assembly) when N > 1 (strong scaling: the frame is fixed).
 `value` = primary rays of the frame / device time per step (CUDA events around every step, the L2 flush between
 steps outside them), max over ranks.  `e2e` goes through the host-buffer C-ABI call (bz_render_host, N = 1) or
 render + gather + device->pinned-host copy of the frame (N > 1, the way home of frame k overlapping the tracing of
@@ -43,6 +43,7 @@ def parse_args():
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="target wall time of one CPU-baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--pipeline", default="auto", choices=["auto", "persistent", "wavefront"], help="how the lens tiles are traced (bz_lens_set_pipeline)")
+    p.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="transport of bz_gather_rows at N > 1 (bz_comm_set_gather)")
     p.add_argument("--mode", default="exact", choices=["exact", "fast"],
                    help="exact: the parity build (-fmad=false, bit-exact with the reference); fast: BZ_MODE_FAST (FMA, MUFU reciprocals; north_star's tolerance)")
     return p.parse_args()
@@ -188,7 +189,9 @@ def main_ours(args, name):
         if world > 1:
             dist.init_process_group("nccl", device_id=torch.device("cuda", local))      # bootstrap + the scalar reductions of this script only
             dist.barrier()
-        comm = sharding.make_comm(bz, local) if world > 1 else None                     # the image gather itself: bz_gather_rows (C ABI, NCCL send / recv to rank 0)
+        comm = sharding.make_comm(bz, local) if world > 1 else None                     # the image gather itself: bz_gather_rows (C ABI)
+        if comm is not None:
+            comm.set_gather(bz.GATHER_NCCL if args.gather == "nccl" else bz.GATHER_PEER)
         torch.cuda.synchronize()
     finally:
         if world > 1:
@@ -230,7 +233,7 @@ def main_ours(args, name):
             rendered_events.append(torch.cuda.Event(enable_timing=True))
             rendered_events[-1].record()
         if world > 1:
-            comm.gather_rows(bands[buf], width, height, stripe, rgba=images[buf])        # NCCL send / recv over NVLink + assembly on rank 0
+            comm.gather_rows(bands[buf], width, height, stripe, rgba=images[buf])        # every rank's rows to rank 0 over NVLink (peer stores, or NCCL send / recv + assembly)
 
     def barrier():
         if world > 1:
@@ -420,11 +423,11 @@ def main_ours(args, name):
                        "l2": "flushed between steps (256 MiB fill, outside the per-step event pairs; flush_ms says what it costs)",
                        "mode": "culled (exact candidate-set-preserving BVH)" + (", BZ_MODE_FAST arithmetic" if args.mode == "fast" else ""), "fmad": args.mode == "fast",
                        "pipeline": args.pipeline, "setup_s": setup_s},
-            "step_split_rank0": split, "flush_ms": flush_ms, "wall_ms_per_step_with_flush": (wall1 - wall0) / args.steps * 1e3,
+            "step_split_rank0": split, "gather": (None if comm is None else ("peer stores into the root's IPC-mapped buffer, generation flags over NVLink (no NCCL call per frame)" if comm.gather_mode() == bz.GATHER_PEER else "ncclSend / ncclRecv + assembly pass")), "flush_ms": flush_ms, "wall_ms_per_step_with_flush": (wall1 - wall0) / args.steps * 1e3,
             "e2e": {"value": frame_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(bz.load().bz_sizeof_camera() + bz.load().bz_sizeof_scene()),
                     "d2h_bytes_per_step": width * height * 4, "ms_per_step": e2e_s * 1e3,
                     "call": "bz_render_host into pinned host memory" if world == 1 else
-                            "bz_render_striped on the compute stream; bz_gather_rows (NCCL send / recv to rank 0) + assembly + D2H to pinned host on a side stream, double-buffered"},
+                            "bz_render_striped on the compute stream; bz_gather_rows (to rank 0 over NVLink) + D2H to pinned host on a side stream, double-buffered"},
             "e2e_moving_camera": {"value": frame_rays / e2e_moving_s / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_moving_s * 1e3, "plan_ms": plan_ms,
                                   "note": "the eye moves by one ulp every step: every frame is planned anew (bz_plan_tiles on the host + upload of the tile list)"},
             "frame_crc32": "%08x" % crc,

@@ -21,6 +21,7 @@ NO_PATCH = 0xFFFFFFFF
 MODE_BRUTE, MODE_CULLED, MODE_LANES, MODE_FAST = 0, 1, 2, 3
 PIPELINE_AUTO, PIPELINE_PERSISTENT, PIPELINE_WAVEFRONT = 0, 1, 2
 ERR_OVERFLOW = -5
+GATHER_PEER, GATHER_NCCL = 0, 1
 PATCH_WORDS = 64
 
 
@@ -151,6 +152,8 @@ SIGNATURES = {
     "bz_comm_create": (_int, [_vp, _u32, _u32, _int, C.POINTER(_vp)]),
     "bz_comm_destroy": (_int, [_vp]),
     "bz_gather_rows": (_int, [_vp, _vp, _u32, _u32, _u32, _u32, _vp, _vp]),
+    "bz_comm_set_gather": (_int, [_vp, _u32]),
+    "bz_comm_gather_mode": (_int, [_vp, C.POINTER(_u32)]),
     "bz_fp32_peak_probe": (_int, [_int, C.POINTER(_f), C.POINTER(_f)]),
     "bz_mesh_create": (_int, [C.POINTER(_vp)]),
     "bz_mesh_destroy": (_int, [_vp]),
@@ -576,6 +579,16 @@ class Comm:
     def gather_rows(self, band, width, height, stripe_rows, rgba=None, root=0, stream=None):
         """every rank: its stripe band (device tensor); root: `rgba` [height, width, 4] gets the assembled frame"""
         _check(self.lib.bz_gather_rows(self.h, _ptr(band), width, height, stripe_rows, root, _ptr(rgba), _stream_handle(stream)))
+
+    def set_gather(self, mode):
+        """GATHER_PEER (default: NVLink stores into the root's buffer) or GATHER_NCCL (send / recv + assembly); same on every rank"""
+        _check(self.lib.bz_comm_set_gather(self.h, mode))
+        return self
+
+    def gather_mode(self):
+        out = _u32(0)
+        _check(self.lib.bz_comm_gather_mode(self.h, C.byref(out)))
+        return int(out.value)
 
     def close(self):
         if getattr(self, "h", None):

@@ -20,6 +20,7 @@
 // only have to be conservative.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <algorithm>
 #include "bz_device.h"
 #include "bz_math.cuh"
 
@@ -442,6 +443,78 @@ __global__ void bz_assemble_kernel(const uint32_t *bands, uint32_t band_rows, ui
   }
 }
 
+// One rank's stripe band -> its rows of the image (bz_gather_rows, peer mode: `image` is the ROOT's buffer, mapped into this process, and
+// the stores travel over NVLink).  One uint4 (four RGBA pixels) per thread when the rows allow it, rows are contiguous so the stores coalesce.
+template<typename WORD>
+__global__ void bz_scatter_band_kernel(const WORD *band, uint32_t rows, uint32_t row_words, uint32_t stripe_rows, uint32_t rank, uint32_t ranks, WORD *image) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if(i < (uint64_t)rows * row_words) {
+    uint32_t local = (uint32_t)(i / row_words), at = (uint32_t)(i - (uint64_t)local * row_words);
+    uint32_t row = ((local / stripe_rows) * ranks + rank) * stripe_rows + local % stripe_rows;
+    image[(uint64_t)row * row_words + at] = band[i];
+  }
+}
+
+// ---- flags of the peer gather (csrc/bz_comm.cu): generation counters in the ROOT's buffer, read and written across NVLink ----
+__device__ __forceinline__ uint32_t bz_load_acquire_sys(const uint32_t *word) {
+  uint32_t value;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(value) : "l"(word) : "memory");
+  return value;
+}
+
+__device__ __forceinline__ void bz_store_release_sys(uint32_t *word, uint32_t value) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(word), "r"(value) : "memory");
+}
+
+// waits until *word >= value (counters only grow); a rank that never answers ends the wait after ten seconds with a trap, which the
+// next CUDA call of this process reports -- a lost rank must not leave the GPU spinning for ever
+__device__ __forceinline__ void bz_wait_word(const uint32_t *word, uint32_t value) {
+  unsigned long long start = 0ull;
+  for(uint32_t spins = 0u; (int32_t)(bz_load_acquire_sys(word) - value) < 0; ++spins) {
+    if((spins & 1023u) == 1023u) {
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if(start == 0ull) { start = now; }
+      else if(now - start > 10000000000ull) { __trap(); }
+    }
+    __nanosleep(200);
+  }
+}
+
+// The scatter of a non-root rank: waits until the root has taken the previous frame out of its buffer (free_word >= need_free), stores the
+// band's rows into their place, and the CTA that finishes last publishes "rows of call `done_value` are there" in the root's buffer.
+template<typename WORD>
+__global__ void bz_scatter_band_flagged_kernel(const WORD *band, uint32_t rows, uint32_t row_words, uint32_t stripe_rows, uint32_t rank, uint32_t ranks, WORD *image,
+                                               const uint32_t *free_word, uint32_t need_free, uint32_t *done_word, uint32_t done_value, uint32_t *finished) {
+  if(threadIdx.x == 0u) { bz_wait_word(free_word, need_free); }
+  __syncthreads();
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if(i < (uint64_t)rows * row_words) {
+    uint32_t local = (uint32_t)(i / row_words), at = (uint32_t)(i - (uint64_t)local * row_words);
+    uint32_t row = ((local / stripe_rows) * ranks + rank) * stripe_rows + local % stripe_rows;
+    image[(uint64_t)row * row_words + at] = band[i];
+  }
+  __threadfence_system();                   // this thread's stores are visible on the root before anything that follows
+  __syncthreads();
+  if(threadIdx.x == 0u) {
+    if(atomicAdd(finished, 1u) == gridDim.x - 1u) {
+      *finished = 0u;                       // (for the next call; calls on one communicator do not overlap)
+      __threadfence_system();
+      bz_store_release_sys(done_word, done_value);
+    }
+  }
+}
+
+// root: one thread per rank waits for that rank's "rows of call `value` are there"
+__global__ void bz_wait_ranks_kernel(const uint32_t *done_words, uint32_t ranks, uint32_t root, uint32_t value) {
+  if(threadIdx.x < ranks && threadIdx.x != root) { bz_wait_word(done_words + threadIdx.x, value); }
+}
+
+__global__ void bz_publish_word_kernel(uint32_t *word, uint32_t value) {
+  __threadfence_system();
+  bz_store_release_sys(word, value);
+}
+
 // K1 alone: primary rays of a row band into n x 3 float arrays (bz_generate_rays).
 __global__ void bz_raygen_kernel(const bz_camera cam, uint32_t row0, uint64_t count, float *start, float *dir) {
   uint64_t id = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -504,6 +577,45 @@ cudaError_t bz_launch_assemble(const uint8_t *bands, uint32_t band_rows, uint32_
   uint64_t const pixels = (uint64_t)width * height;
   if(pixels == 0u) { return cudaSuccess; }
   bz_assemble_kernel<<<(unsigned)((pixels + 255u) / 256u), 256, 0, stream>>>((const uint32_t*)bands, band_rows, width, height, stripe_rows, ranks, (uint32_t*)image);
+  return cudaGetLastError();
+}
+
+cudaError_t bz_launch_scatter_band(const uint8_t *band, uint32_t rows, uint32_t width, uint32_t stripe_rows, uint32_t rank, uint32_t ranks,
+                                   uint8_t *image, cudaStream_t stream) {
+  if((uint64_t)rows * width == 0u) { return cudaSuccess; }
+  if(width % 4u == 0u && ((uintptr_t)band | (uintptr_t)image) % 16u == 0u) {
+    uint64_t const words = (uint64_t)rows * (width / 4u);
+    bz_scatter_band_kernel<uint4><<<(unsigned)((words + 255u) / 256u), 256, 0, stream>>>((const uint4*)band, rows, width / 4u, stripe_rows, rank, ranks, (uint4*)image);
+  }
+  else {
+    uint64_t const words = (uint64_t)rows * width;
+    bz_scatter_band_kernel<uint32_t><<<(unsigned)((words + 255u) / 256u), 256, 0, stream>>>((const uint32_t*)band, rows, width, stripe_rows, rank, ranks, (uint32_t*)image);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t bz_launch_scatter_band_flagged(const uint8_t *band, uint32_t rows, uint32_t width, uint32_t stripe_rows, uint32_t rank, uint32_t ranks, uint8_t *image,
+                                           const uint32_t *free_word, uint32_t need_free, uint32_t *done_word, uint32_t done_value, uint32_t *finished, cudaStream_t stream) {
+  if(width % 4u == 0u && ((uintptr_t)band | (uintptr_t)image) % 16u == 0u) {
+    uint64_t const words = (uint64_t)rows * (width / 4u);
+    bz_scatter_band_flagged_kernel<uint4><<<(unsigned)std::max<uint64_t>(1u, (words + 255u) / 256u), 256, 0, stream>>>((const uint4*)band, rows, width / 4u, stripe_rows, rank, ranks,
+                                                                                                         (uint4*)image, free_word, need_free, done_word, done_value, finished);
+  }
+  else {
+    uint64_t const words = (uint64_t)rows * width;
+    bz_scatter_band_flagged_kernel<uint32_t><<<(unsigned)std::max<uint64_t>(1u, (words + 255u) / 256u), 256, 0, stream>>>((const uint32_t*)band, rows, width, stripe_rows, rank, ranks,
+                                                                                                            (uint32_t*)image, free_word, need_free, done_word, done_value, finished);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t bz_launch_wait_ranks(const uint32_t *done_words, uint32_t ranks, uint32_t root, uint32_t value, cudaStream_t stream) {
+  bz_wait_ranks_kernel<<<1, 1024, 0, stream>>>(done_words, ranks, root, value);
+  return cudaGetLastError();
+}
+
+cudaError_t bz_launch_publish_word(uint32_t *word, uint32_t value, cudaStream_t stream) {
+  bz_publish_word_kernel<<<1, 1, 0, stream>>>(word, value);
   return cudaGetLastError();
 }
 

@@ -253,8 +253,17 @@ int  bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *s
  * a file, torch.distributed); every rank then calls bz_comm_create with its rank -- a collective call (ncclCommInitRank).  NCCL is
  * loaded at run time; without it these calls return BZ_ERR_COMM and everything else still works.
  * bz_gather_rows: every rank passes its band of bz_render_striped (bz_striped_rows(height, stripe_rows, rank, ranks) rows); the root
- * receives the bands over NVLink / NVSwitch (ncclSend / ncclRecv, one group) and assembles d_rgba = height x width x 4 bytes in image
- * order; d_rgba is ignored on the other ranks.  Asynchronous on `stream` on every rank. */
+ * ends up with d_rgba = height x width x 4 bytes in image order; d_rgba is ignored on the other ranks.  Asynchronous on `stream` on
+ * every rank; every rank of the communicator calls it with the same width, height, stripe_rows and root.  Two transports:
+ *   BZ_GATHER_PEER  (default) the root keeps an image buffer that the other ranks map (CUDA IPC); each rank's rows are STORED straight into
+ *                   their place in it over NVLink / NVSwitch by one kernel per rank -- transfer and assembly fused, all ranks in parallel.
+ *                   "Rows of call k are there" and "frame k has been taken out of the buffer" are generation counters in that buffer,
+ *                   written and polled across NVLink by the same kernels: no NCCL call per frame.  The first call with a new frame size
+ *                   or root sets the mapping up (collective: NCCL broadcast of the IPC handle, synchronises the stream); if IPC mapping
+ *                   fails on any rank, all ranks fall back to BZ_GATHER_NCCL together (bz_comm_gather_mode tells which is in use).  A rank
+ *                   that waits ten seconds for another rank's flag traps (the next CUDA call reports it) instead of spinning for ever.
+ *   BZ_GATHER_NCCL  bands by ncclSend / ncclRecv (one group) into a staging buffer on the root, then one pass that puts the rows in place.
+ * bz_comm_set_gather: same mode on every rank, between calls. */
 #define BZ_COMM_ID_BYTES 128
 typedef struct bz_comm bz_comm;
 int  bz_comm_unique_id(uint8_t out_id[BZ_COMM_ID_BYTES]);
@@ -262,6 +271,10 @@ int  bz_comm_create(const uint8_t id[BZ_COMM_ID_BYTES], uint32_t rank, uint32_t 
 int  bz_comm_destroy(bz_comm *comm);
 int  bz_gather_rows(bz_comm *comm, const uint8_t *d_band, uint32_t width, uint32_t height, uint32_t stripe_rows, uint32_t root,
                     uint8_t *d_rgba, void *stream);
+#define BZ_GATHER_PEER 0u
+#define BZ_GATHER_NCCL 1u
+int  bz_comm_set_gather(bz_comm *comm, uint32_t mode);
+int  bz_comm_gather_mode(const bz_comm *comm, uint32_t *out_mode);
 
 /* After an all-gather of the ranks' stripe buffers (each padded to band_rows rows; NCCL over NVLink in bench.py):
  * d_bands = ranks x band_rows x width x 4 bytes -> d_rgba = height x width x 4 bytes in image order. */

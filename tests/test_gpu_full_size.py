@@ -66,21 +66,29 @@ def test_cfg4_stripes_equal_whole_frame(oracle_built):
 
 
 def test_gather_rows_through_the_c_abi_single_rank(oracle_built):
-    """bz_comm_* + bz_gather_rows (NCCL loaded at run time) with a communicator of one rank: the root's own band goes through the
-    same staging and assembly as the received ones.  Several ranks are exercised by bench.py under torchrun, whose frame_crc32
-    must equal the single-GPU one (profiles/, SCALE); the stripe arithmetic itself is covered on the CPU (tests/test_sharding_gloo.py)."""
+    """bz_comm_* + bz_gather_rows (NCCL loaded at run time) with a communicator of one rank, both transports: the root's own band goes
+    through the same scatter into the root's buffer (BZ_GATHER_PEER) or staging and assembly (BZ_GATHER_NCCL) as the other ranks' rows,
+    twice in a row and after a change of the frame size (the peer buffer is set up anew).  Several ranks are exercised by bench.py under
+    torchrun, whose frame_crc32 must equal the single-GPU one (profiles/, SCALE); the stripe arithmetic itself is covered on the CPU
+    (tests/test_sharding_gloo.py)."""
     import torch
     import bezier_b200 as bz
     from bezier_b200 import workloads
     spec, mesh, cam_kw, scene_kw = workloads.setup("cfg1_sphere_640x480", bz.Mesh)
     lens = bz.BezierLens(spec["ri"], bz.BezierMesh(mesh))
-    cam, scene = bz.make_camera(spec["width"], spec["height"], **cam_kw), bz.make_scene(**scene_kw)
-    full, _ = lens.render(cam, scene)
+    scene = bz.make_scene(**scene_kw)
     comm = bz.Comm(0, 1, 0, lambda ident: ident)
-    band = torch.zeros((cam.height, cam.width, 4), dtype=torch.uint8, device="cuda")
-    image = torch.zeros_like(band)
-    lens.render_striped_device(cam, scene, workloads.STRIPE_ROWS, 0, 1, band)
-    comm.gather_rows(band, cam.width, cam.height, workloads.STRIPE_ROWS, rgba=image)
-    torch.cuda.synchronize()
-    assert np.array_equal(image.cpu().numpy(), full)
+    assert comm.gather_mode() == bz.GATHER_PEER
+    for mode in (bz.GATHER_PEER, bz.GATHER_NCCL):
+        comm.set_gather(mode)
+        for width, height in ((spec["width"], spec["height"]), (spec["width"], spec["height"]), (322, 243)):
+            cam = bz.make_camera(width, height, **cam_kw)
+            full, _ = lens.render(cam, scene)
+            band = torch.zeros((cam.height, cam.width, 4), dtype=torch.uint8, device="cuda")
+            image = torch.zeros_like(band)
+            lens.render_striped_device(cam, scene, workloads.STRIPE_ROWS, 0, 1, band)
+            comm.gather_rows(band, cam.width, cam.height, workloads.STRIPE_ROWS, rgba=image)
+            torch.cuda.synchronize()
+            assert np.array_equal(image.cpu().numpy(), full), (mode, width, height)
+        assert comm.gather_mode() == mode
     comm.close()

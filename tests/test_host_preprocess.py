@@ -193,4 +193,6 @@ def test_comm_argument_checks():
     assert lib.bz_comm_create(ident, 3, 2, 0, C.byref(handle)) == bz.ERR_INVALID      # rank >= ranks
     assert lib.bz_comm_create(None, 0, 1, 0, C.byref(handle)) == bz.ERR_INVALID
     assert lib.bz_gather_rows(None, None, 4, 4, 8, 0, None, None) == bz.ERR_INVALID
+    assert lib.bz_comm_set_gather(None, 0) == bz.ERR_INVALID
+    assert lib.bz_comm_gather_mode(None, None) == bz.ERR_INVALID
     assert lib.bz_comm_destroy(None) == bz.OK
