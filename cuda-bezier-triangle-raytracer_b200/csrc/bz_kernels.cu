@@ -466,7 +466,7 @@ __device__ __forceinline__ void bz_store_release_sys(uint32_t *word, uint32_t va
   asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(word), "r"(value) : "memory");
 }
 
-// waits until *word >= value (counters only grow); a rank that never answers ends the wait after ten seconds with a trap, which the
+// waits until *word >= value (counters only grow); a rank that never answers ends the wait after two minutes with a trap, which the
 // next CUDA call of this process reports -- a lost rank must not leave the GPU spinning for ever
 __device__ __forceinline__ void bz_wait_word(const uint32_t *word, uint32_t value) {
   unsigned long long start = 0ull;
@@ -475,7 +475,7 @@ __device__ __forceinline__ void bz_wait_word(const uint32_t *word, uint32_t valu
       unsigned long long now;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
       if(start == 0ull) { start = now; }
-      else if(now - start > 10000000000ull) { __trap(); }
+      else if(now - start > 120000000000ull) { __trap(); }
     }
     __nanosleep(200);
   }

@@ -261,7 +261,7 @@ int  bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *s
  *                   written and polled across NVLink by the same kernels: no NCCL call per frame.  The first call with a new frame size
  *                   or root sets the mapping up (collective: NCCL broadcast of the IPC handle, synchronises the stream); if IPC mapping
  *                   fails on any rank, all ranks fall back to BZ_GATHER_NCCL together (bz_comm_gather_mode tells which is in use).  A rank
- *                   that waits ten seconds for another rank's flag traps (the next CUDA call reports it) instead of spinning for ever.
+ *                   that waits two minutes for another rank's flag traps (the next CUDA call reports it) instead of spinning for ever.
  *   BZ_GATHER_NCCL  bands by ncclSend / ncclRecv (one group) into a staging buffer on the root, then one pass that puts the rows in place.
  * bz_comm_set_gather: same mode on every rank, between calls. */
 #define BZ_COMM_ID_BYTES 128
