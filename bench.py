@@ -447,7 +447,11 @@ def main_ours(args, name):
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
-        comm.close()
+        if rank != 0:
+            comm.close()                   # the other ranks unmap the root's frame buffer ...
+        dist.barrier()
+        if rank == 0:
+            comm.close()                   # ... before the root frees it (include/bz_capi.h: bz_comm_destroy)
         dist.destroy_process_group()
 
 
