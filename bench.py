@@ -447,11 +447,7 @@ def main_ours(args, name):
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
-        if rank != 0:
-            comm.close()                   # the other ranks unmap the root's frame buffer ...
-        dist.barrier()
-        if rank == 0:
-            comm.close()                   # ... before the root frees it (include/bz_capi.h: bz_comm_destroy)
+        comm.close()                       # every rank: bz_comm_destroy is collective (ncclCommDestroy waits for the other ranks)
         dist.destroy_process_group()
 
 

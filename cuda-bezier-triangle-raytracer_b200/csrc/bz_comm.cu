@@ -274,13 +274,15 @@ int bz_comm_destroy(bz_comm *comm) {
   cudaDeviceSynchronize();
   cudaFree(comm->d_bands);
   cudaFree(comm->d_token);
-  if(comm->d_image != nullptr) {
-    if(comm->rank == comm->image_root) { cudaFree(comm->d_image); }
-    else { cudaIpcCloseMemHandle(comm->d_image); }
-  }
-  for(void *p : comm->retired) { cudaFree(p); }
+  // the ranks that map the root's frame buffer let go of it BEFORE the communicator's teardown (where NCCL makes the ranks meet), the
+  // root frees it after
+  bool const owner = (comm->d_image != nullptr && comm->rank == comm->image_root);
+  if(comm->d_image != nullptr && !owner) { cudaIpcCloseMemHandle(comm->d_image); }
   cudaGetLastError();
   if(comm->comm != nullptr) { nccl().commDestroy(comm->comm); }
+  if(owner) { cudaFree(comm->d_image); }
+  for(void *p : comm->retired) { cudaFree(p); }
+  cudaGetLastError();
   delete comm;
   return BZ_OK;
 }

@@ -263,8 +263,9 @@ int  bz_render_striped(bz_lens *lens, const bz_camera *camera, const bz_scene *s
  *                   fails on any rank, all ranks fall back to BZ_GATHER_NCCL together (bz_comm_gather_mode tells which is in use).  A rank
  *                   that waits two minutes for another rank's flag traps (the next CUDA call reports it) instead of spinning for ever.
  *   BZ_GATHER_NCCL  bands by ncclSend / ncclRecv (one group) into a staging buffer on the root, then one pass that puts the rows in place.
- * bz_comm_set_gather: same mode on every rank, between calls.  bz_comm_destroy: after the last gather has completed on every rank; the root
- * of BZ_GATHER_PEER owns the mapped buffer, so destroy its communicator last (bench.py: the others, a barrier, then the root). */
+ * bz_comm_set_gather: same mode on every rank, between calls.  bz_comm_destroy: collective like bz_comm_create -- every rank calls it, after
+ * its last gather has completed (ncclCommDestroy waits for the other ranks; a rank that waits alone for the others before destroying
+ * deadlocks).  The other ranks unmap the root's buffer before that meeting point, the root frees it after. */
 #define BZ_COMM_ID_BYTES 128
 typedef struct bz_comm bz_comm;
 int  bz_comm_unique_id(uint8_t out_id[BZ_COMM_ID_BYTES]);

@@ -5,7 +5,7 @@ N=$1
 X=${2:-}
 T=$(echo "$X" | tr -d ' -')
 mkdir -p gpurun_out/r02
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 20 --warmup 5 $X > gpurun_out/r02/bench_cfg4_n$N$T.json 2> gpurun_out/r02/bench_n$N$T.err; echo "bench n$N $X rc=$?"; tail -3 gpurun_out/r02/bench_n$N$T.err
+timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 20 --warmup 5 $X > gpurun_out/r02/bench_cfg4_n$N$T.json 2> gpurun_out/r02/bench_n$N$T.err; echo "bench n$N $X rc=$?"; tail -3 gpurun_out/r02/bench_n$N$T.err
 python - <<PY
 import json
 d=json.loads(open("gpurun_out/r02/bench_cfg4_n$N$T.json").read().strip().splitlines()[-1])
