@@ -33,7 +33,7 @@ def gather_bands(band, bands_out=None):
 
 def make_comm(bz, device):
     """bz.Comm over the ranks of the initialised torch.distributed group: torch only carries the 128-byte id (bootstrap), the
-    gather itself is bz_gather_rows in the C ABI (ncclSend / ncclRecv to the root)"""
+    gather itself is bz_gather_rows in the C ABI (peer stores into the root's IPC-mapped frame, or ncclSend / ncclRecv to the root)"""
     import torch
     import torch.distributed as dist
     rank, world = (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
