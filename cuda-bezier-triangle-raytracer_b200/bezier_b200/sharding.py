@@ -2,8 +2,9 @@
 
 The frame is cut into stripes of `stripe_rows` rows dealt round-robin to the ranks; every rank renders its stripes into
 a compact band buffer (bz_render_striped).  Rays are independent, so the only exchange is the image gather at the end:
-one all-gather of equally sized (padded) bands -- NCCL over NVLink on the GPUs, gloo in the CPU tests -- followed by
-bz_assemble_stripes on the device.  Tables are replicated: every rank builds the same lens from the same mesh."""
+on the GPUs bz_gather_rows of the C ABI (make_comm below: every rank stores its rows into the root's frame over NVLink);
+the helpers here are the host-side arithmetic of the layout and an all-gather form of the same exchange (gloo in the CPU
+tests, followed by bz_assemble_stripes' arithmetic).  Tables are replicated: every rank builds the same lens from the same mesh."""
 import numpy as np
 
 
